@@ -1,0 +1,182 @@
+/* include/rt_api.h -- C ABI of the B200-native path-tracing backend (librtiow_b200.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of Alabuta/RaytracingInOneWeekend:
+ *   camera rays -> sphere closest-hit -> material bounce loop -> accumulate / gamma / 8-bit.
+ * Plain pointers and sizes only; no C++/torch types; no exception crosses this boundary and the
+ * library never calls cudaDeviceReset (the reference does: src/CUDA/cuda_impl.cu:101-114).
+ *
+ * Reference interface each entry point replaces (paths relative to the reference repo):
+ *   rt_scene_upload    <- raytracer::data{spheres,materials}            src/raytracer.hxx:19-30
+ *                         primitives::sphere{center,radius,material_index} src/primitives.hxx:6-17
+ *                         material::{lambert,metal,dielectric}           src/material.hxx:12-41
+ *                         (hard-coded device copies in src/CUDA/cuda_impl.cu:404-417)
+ *   rt_camera_set      <- raytracer::camera ctor                        src/camera.hxx:24-44
+ *   rt_render          <- the pixel/sample loop + app::color            src/main.cxx:52-75,191-207
+ *                         (GPU twin: cuda::data::render                 src/CUDA/cuda_impl.cu:361-380)
+ *   rt_primary_hits    <- raytracer::hit_world / intersect              src/raytracer.hxx:52-118
+ *   rt_readback_rgb8   <- gamma_correction + normalize_rgb_to_8bit      src/main.cxx:39-45,77-85,207-213
+ *                         (GPU twin: rgb32_to_rgb8 + thrust::copy       src/CUDA/cuda_impl.cu:85-99,449-452)
+ *   rt_render_frame    <- void cuda_impl(width, height, image_texels)   src/main.cxx:18,114;
+ *                                                                       src/CUDA/cuda_impl.cu:384-453
+ *   rt_write_ppm       <- app::save_to_file                             src/main.cxx:87-101
+ *
+ * Threading: one rt_ctx per GPU per process; calls on one ctx are serialised by the caller.
+ * Every function returns RT_OK (0) or a negative rt_status; rt_last_error() gives the text.
+ * There is NO CPU fallback: without a usable CUDA device rt_create fails.
+ */
+#ifndef RT_API_H
+#define RT_API_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define RT_EXPORT __declspec(dllexport)
+#else
+#define RT_EXPORT __attribute__((visibility("default")))
+#endif
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,   /* bad argument / call order */
+    RT_ERR_CUDA = -2,      /* a CUDA runtime call failed */
+    RT_ERR_NO_DEVICE = -3, /* no usable CUDA device: the backend refuses to run */
+    RT_ERR_IO = -4,
+    RT_ERR_SYS = -5
+} rt_status;
+
+enum { RT_LAMBERT = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
+
+/* rt_render_params.flags / rt_primary_hits flags */
+enum {
+    RT_FLAG_EXACT = 1u << 0,      /* parity mode: no FMA contraction, the reference's operation order */
+    RT_FLAG_ACCEL_BRUTE = 1u << 1,/* force brute-force closest hit (spheres staged in shared memory) */
+    RT_FLAG_ACCEL_LBVH = 1u << 2  /* force the GPU-built LBVH */
+    /* neither accel flag: brute force up to RT_BRUTE_MAX_SPHERES, LBVH above */
+};
+#define RT_BRUTE_MAX_SPHERES 8192u
+
+typedef struct rt_ctx rt_ctx;
+
+/* primitives::sphere (src/primitives.hxx:6-17); a negative radius flips the normal (hollow glass). */
+typedef struct rt_sphere { float cx, cy, cz, r; uint32_t mat; } rt_sphere;
+
+/* material::types (src/material.hxx:12-51).  param = roughness (metal) | refraction_index (dielectric). */
+typedef struct rt_material { float r, g, b, param; uint32_t kind; } rt_material;
+
+typedef struct rt_tile { uint32_t x0, y0, w, h; } rt_tile;
+
+typedef struct rt_render_params {
+    uint32_t spp;          /* camera paths per pixel added by this call */
+    uint32_t max_depth;    /* bounce cap (reference: 64 on CPU, src/raytracer.hxx:20; BASELINE: 50) */
+    uint64_t seed;         /* Philox key */
+    uint32_t sample_base;  /* first sample index; samples [sample_base, sample_base+spp) are traced */
+    uint32_t flags;        /* RT_FLAG_* */
+} rt_render_params;
+
+typedef struct rt_stats {
+    uint64_t samples;      /* camera paths traced since rt_stats_reset */
+    uint64_t segments;     /* closest-hit queries (hit_world calls) */
+    uint64_t sphere_tests; /* brute force: segments * n_spheres; LBVH: leaf sphere tests */
+    uint64_t node_visits;  /* LBVH inner-node visits */
+    uint64_t sky;          /* paths that reached the background */
+    uint64_t absorbed;     /* metal scatter below the surface (returns black) */
+    uint64_t capped;       /* paths cut by max_depth (returns black) */
+    uint64_t launches;     /* kernels launched by this library */
+    double render_ms;      /* device time of the render kernels (CUDA events), cumulative */
+    double last_render_ms; /* device time of the most recent rt_render */
+    double bvh_build_ms;   /* device time of the most recent LBVH build */
+} rt_stats;
+
+RT_EXPORT const char *rt_last_error(void);
+RT_EXPORT const char *rt_version(void);
+
+/* device = CUDA ordinal (e.g. LOCAL_RANK).  Fails with RT_ERR_NO_DEVICE if CUDA is unusable. */
+RT_EXPORT int rt_create(rt_ctx **out, int device);
+RT_EXPORT int rt_destroy(rt_ctx *ctx);
+
+/* Use an existing CUDA stream (e.g. torch's current stream); NULL restores the ctx's own stream. */
+RT_EXPORT int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
+RT_EXPORT int rt_sync(rt_ctx *ctx);
+
+/* Scene: converted on the host to the device layout (float4{c,r*r} + radius + material index;
+ * float4{albedo,param} + kind) and uploaded; builds the LBVH when n > RT_BRUTE_MAX_SPHERES or
+ * when it is later requested by flag. */
+RT_EXPORT int rt_scene_upload(rt_ctx *ctx, const rt_sphere *spheres, uint32_t n,
+                              const rt_material *materials, uint32_t m);
+
+/* Camera: the constructor arguments of src/camera.hxx:24; derived vectors computed on the host with
+ * the reference's float operation order.  rt_camera_get returns
+ * {origin[3], lower_left_corner[3], horizontal[3], vertical[3], lens_radius}. */
+RT_EXPORT int rt_camera_set(rt_ctx *ctx, const float pos[3], const float lookat[3], const float up[3],
+                            float aspect, float vfov_deg, float aperture, float focus_dist);
+RT_EXPORT int rt_camera_get(rt_ctx *ctx, float out13[13]);
+
+/* Framebuffer: W x H accumulators of 4 x uint64 {R,G,B (32.32 fixed point sums), sample count}.
+ * (Re)allocates if the size changes and clears. */
+RT_EXPORT int rt_framebuffer(rt_ctx *ctx, uint32_t width, uint32_t height);
+RT_EXPORT int rt_clear(rt_ctx *ctx);
+
+/* Trace params->spp camera paths for every pixel of `tile` and ADD them to the accumulators.
+ * Asynchronous on the ctx stream; rt_sync / any readback waits. */
+RT_EXPORT int rt_render(rt_ctx *ctx, const rt_tile *tile, const rt_render_params *params);
+
+/* Parity pass (BASELINE config 2): primary rays, u = x/W, v = y/H, no jitter, no lens offset.
+ * Host outputs, tile-shaped (h rows of w): sphere index (-1 = miss), t, normal xyz (0 on miss). */
+RT_EXPORT int rt_primary_hits(rt_ctx *ctx, const rt_tile *tile, uint32_t flags,
+                              int32_t *sphere_index, float *t, float *normal_xyz);
+
+/* Closest hit for caller-supplied rays (n x {o[3], d[3]}), host in / host out. */
+RT_EXPORT int rt_closest_hits(rt_ctx *ctx, const float *rays6, uint64_t n, uint32_t flags,
+                              int32_t *sphere_index, float *t, float *normal_xyz);
+
+/* Resolve: mean = sum / count -> powf(mean, 1/2.2f) -> (uint8)(255*c), tightly packed RGB, row-major,
+ * top row first (the reference's texel layout, src/main.cxx:96-100).  dst is HOST memory, W*H*3. */
+RT_EXPORT int rt_readback_rgb8(rt_ctx *ctx, uint8_t *dst);
+/* Mean linear radiance, W*H*3 float, HOST memory. */
+RT_EXPORT int rt_readback_f32(rt_ctx *ctx, float *dst);
+/* Raw accumulators, W*H*4 uint64 {R,G,B,count}, HOST memory (bit-exact parity tests). */
+RT_EXPORT int rt_readback_accum(rt_ctx *ctx, uint64_t *dst);
+
+/* Device-side handles for host plumbing (NCCL gather of the framebuffer through torch.distributed):
+ *   accum : W*H*4 uint64 accumulators;  rgb8 : W*H*3 bytes, written by rt_resolve_device. */
+RT_EXPORT int rt_device_accum(rt_ctx *ctx, void **dptr, size_t *bytes);
+RT_EXPORT int rt_device_rgb8(rt_ctx *ctx, void **dptr, size_t *bytes);
+/* Resolve into the device rgb8 buffer without copying to the host.  Pixels with count == 0 give 0. */
+RT_EXPORT int rt_resolve_device(rt_ctx *ctx);
+
+/* The whole reference-facing call in one: upload scene + camera, render the full W x H image at
+ * spp / max_depth, resolve, copy RGB8 to the HOST buffer.  This is cuda_impl() with the scene made an
+ * argument; host->device and device->host copies are inside. */
+RT_EXPORT int rt_render_frame(rt_ctx *ctx, const rt_sphere *spheres, uint32_t n,
+                              const rt_material *materials, uint32_t m, const float camera13[13],
+                              uint32_t width, uint32_t height, const rt_render_params *params,
+                              uint8_t *rgb8_out);
+
+RT_EXPORT int rt_stats_get(rt_ctx *ctx, rt_stats *out);
+RT_EXPORT int rt_stats_reset(rt_ctx *ctx);
+
+/* P6 writer with the reference's exact header format (src/main.cxx:96). */
+RT_EXPORT int rt_write_ppm(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8);
+
+/* FP32 FMA-chain microbenchmark: the measured denominator of the FP32 roofline.
+ * out = {TFLOP/s achieved (FMA = 2 flop), kernel ms, SM count}. */
+RT_EXPORT int rt_fp32_peak_probe(rt_ctx *ctx, double out3[3]);
+
+/* ---- node-level tile queue (multi-GPU dynamic tile stealing, one process per GPU) -------------
+ * A lock-free counter in POSIX shared memory, shared by the ranks of one node.  Rank 0 creates,
+ * the others open.  rt_queue_next returns the previous value after adding `n` (fetch_add). */
+typedef struct rt_queue rt_queue;
+RT_EXPORT int rt_queue_open(rt_queue **out, const char *name, int create);
+RT_EXPORT int rt_queue_reset(rt_queue *q, uint64_t value);
+RT_EXPORT int rt_queue_next(rt_queue *q, uint64_t n, uint64_t *previous);
+RT_EXPORT int rt_queue_close(rt_queue *q, int unlink_name);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_API_H */

@@ -1,0 +1,294 @@
+"""ctypes binding of librtiow_b200.so (include/rt_api.h) -- the Python face of the C ABI.
+
+This is plumbing for tests, bench.py and the torch.distributed multi-GPU driver; the product is the
+CUDA library.  There is NO fallback: if the shared library is missing or no sm_100 GPU is usable,
+construction raises.  Nothing here imports anything under ``oracle/``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librtiow_b200.so")
+
+FLAG_EXACT = 1 << 0
+FLAG_BRUTE = 1 << 1
+FLAG_LBVH = 1 << 2
+
+EXPORTS = [
+    "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync",
+    "rt_scene_upload", "rt_camera_set", "rt_camera_get", "rt_framebuffer", "rt_clear", "rt_render",
+    "rt_primary_hits", "rt_closest_hits", "rt_readback_rgb8", "rt_readback_f32", "rt_readback_accum",
+    "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
+    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe",
+    "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
+]
+
+
+class RtSphere(C.Structure):
+    _fields_ = [("cx", C.c_float), ("cy", C.c_float), ("cz", C.c_float), ("r", C.c_float), ("mat", C.c_uint32)]
+
+
+class RtMaterial(C.Structure):
+    _fields_ = [("r", C.c_float), ("g", C.c_float), ("b", C.c_float), ("param", C.c_float), ("kind", C.c_uint32)]
+
+
+class RtTile(C.Structure):
+    _fields_ = [("x0", C.c_uint32), ("y0", C.c_uint32), ("w", C.c_uint32), ("h", C.c_uint32)]
+
+
+class RtRenderParams(C.Structure):
+    _fields_ = [("spp", C.c_uint32), ("max_depth", C.c_uint32), ("seed", C.c_uint64),
+                ("sample_base", C.c_uint32), ("flags", C.c_uint32)]
+
+
+class RtStats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("segments", C.c_uint64), ("sphere_tests", C.c_uint64),
+                ("node_visits", C.c_uint64), ("sky", C.c_uint64), ("absorbed", C.c_uint64),
+                ("capped", C.c_uint64), ("launches", C.c_uint64), ("render_ms", C.c_double),
+                ("last_render_ms", C.c_double), ("bvh_build_ms", C.c_double)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+SPHERE_DTYPE = np.dtype([("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"), ("r", "<f4"), ("mat", "<u4")])
+MATERIAL_DTYPE = np.dtype([("r", "<f4"), ("g", "<f4"), ("b", "<f4"), ("param", "<f4"), ("kind", "<u4")])
+
+
+class RtError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH) -> C.CDLL:
+    """Load the C-ABI library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise RtError(f"{path} is missing: build it with `make -C {HERE}` (or __graft_entry__.build()); "
+                      "there is no CPU fallback")
+    lib = C.CDLL(path)
+    vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
+    fp = C.POINTER(C.c_float)
+    lib.rt_last_error.restype = C.c_char_p
+    lib.rt_version.restype = C.c_char_p
+    lib.rt_create.argtypes = [C.POINTER(vp), i32]
+    lib.rt_destroy.argtypes = [vp]
+    lib.rt_set_stream.argtypes = [vp, vp]
+    lib.rt_sync.argtypes = [vp]
+    lib.rt_scene_upload.argtypes = [vp, vp, u32, vp, u32]
+    lib.rt_camera_set.argtypes = [vp, fp, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float]
+    lib.rt_camera_get.argtypes = [vp, fp]
+    lib.rt_framebuffer.argtypes = [vp, u32, u32]
+    lib.rt_clear.argtypes = [vp]
+    lib.rt_render.argtypes = [vp, C.POINTER(RtTile), C.POINTER(RtRenderParams)]
+    lib.rt_primary_hits.argtypes = [vp, C.POINTER(RtTile), u32, vp, vp, vp]
+    lib.rt_closest_hits.argtypes = [vp, vp, u64, u32, vp, vp, vp]
+    lib.rt_readback_rgb8.argtypes = [vp, vp]
+    lib.rt_readback_f32.argtypes = [vp, vp]
+    lib.rt_readback_accum.argtypes = [vp, vp]
+    lib.rt_device_accum.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
+    lib.rt_device_rgb8.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
+    lib.rt_resolve_device.argtypes = [vp]
+    lib.rt_render_frame.argtypes = [vp, vp, u32, vp, u32, fp, u32, u32, C.POINTER(RtRenderParams), vp]
+    lib.rt_stats_get.argtypes = [vp, C.POINTER(RtStats)]
+    lib.rt_stats_reset.argtypes = [vp]
+    lib.rt_write_ppm.argtypes = [C.c_char_p, u32, u32, vp]
+    lib.rt_fp32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
+    lib.rt_queue_open.argtypes = [C.POINTER(vp), C.c_char_p, i32]
+    lib.rt_queue_reset.argtypes = [vp, u64]
+    lib.rt_queue_next.argtypes = [vp, u64, C.POINTER(u64)]
+    lib.rt_queue_close.argtypes = [vp, i32]
+    for name in EXPORTS:
+        fn = getattr(lib, name)
+        if name not in ("rt_last_error", "rt_version"):
+            fn.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc):
+    if rc != 0:
+        raise RtError(f"rt error {rc}: {lib.rt_last_error().decode()}")
+
+
+def pack_scene(scene):
+    """scenes.Scene -> (rt_sphere[n], rt_material[m]) structured arrays."""
+    sph = np.zeros(scene.n, SPHERE_DTYPE)
+    sph["cx"], sph["cy"], sph["cz"], sph["r"] = scene.spheres.T
+    sph["mat"] = scene.sphere_mat
+    mat = np.zeros(scene.m, MATERIAL_DTYPE)
+    mat["r"], mat["g"], mat["b"], mat["param"] = scene.materials.T
+    mat["kind"] = scene.mat_kind
+    return sph, mat
+
+
+class Backend:
+    """One rt_ctx on one GPU."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.ctx = C.c_void_p()
+        _check(self.lib, self.lib.rt_create(C.byref(self.ctx), int(device)))
+        self.device = device
+        self.W = self.H = 0
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.rt_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- scene / camera / framebuffer ---------------------------------------
+    def upload_scene(self, scene):
+        sph, mat = pack_scene(scene)
+        _check(self.lib, self.lib.rt_scene_upload(self.ctx, sph.ctypes.data, sph.shape[0], mat.ctypes.data, mat.shape[0]))
+        self.set_camera(scene.camera)
+
+    def set_camera(self, cam13):
+        cam = np.ascontiguousarray(cam13, np.float32)
+        fp = C.POINTER(C.c_float)
+        pos, lookat, up = cam[0:3].copy(), cam[3:6].copy(), cam[6:9].copy()
+        _check(self.lib, self.lib.rt_camera_set(self.ctx, pos.ctypes.data_as(fp), lookat.ctypes.data_as(fp),
+                                                 up.ctypes.data_as(fp),
+                                                 float(cam[9]), float(cam[10]), float(cam[11]), float(cam[12])))
+
+    def camera_state(self):
+        out = np.zeros(13, np.float32)
+        _check(self.lib, self.lib.rt_camera_get(self.ctx, out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
+    def framebuffer(self, W, H):
+        _check(self.lib, self.lib.rt_framebuffer(self.ctx, int(W), int(H)))
+        self.W, self.H = int(W), int(H)
+
+    def clear(self):
+        _check(self.lib, self.lib.rt_clear(self.ctx))
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(self.lib, self.lib.rt_set_stream(self.ctx, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        _check(self.lib, self.lib.rt_sync(self.ctx))
+
+    # ---- rendering ----------------------------------------------------------
+    def render(self, spp, max_depth=50, seed=1, tile=None, sample_base=0, flags=0):
+        x0, y0, w, h = tile if tile is not None else (0, 0, self.W, self.H)
+        t = RtTile(x0, y0, w, h)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
+        _check(self.lib, self.lib.rt_render(self.ctx, C.byref(t), C.byref(p)))
+
+    def primary_hits(self, tile=None, flags=FLAG_EXACT):
+        x0, y0, w, h = tile if tile is not None else (0, 0, self.W, self.H)
+        t = RtTile(x0, y0, w, h)
+        idx = np.zeros((h, w), np.int32)
+        tt = np.zeros((h, w), np.float32)
+        nrm = np.zeros((h, w, 3), np.float32)
+        _check(self.lib, self.lib.rt_primary_hits(self.ctx, C.byref(t), int(flags), idx.ctypes.data, tt.ctypes.data, nrm.ctypes.data))
+        return idx, tt, nrm
+
+    def closest_hits(self, rays, flags=FLAG_EXACT):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        idx = np.zeros(n, np.int32)
+        tt = np.zeros(n, np.float32)
+        nrm = np.zeros((n, 3), np.float32)
+        _check(self.lib, self.lib.rt_closest_hits(self.ctx, rays.ctypes.data, n, int(flags), idx.ctypes.data, tt.ctypes.data, nrm.ctypes.data))
+        return idx, tt, nrm
+
+    def readback_rgb8(self):
+        out = np.zeros((self.H, self.W, 3), np.uint8)
+        _check(self.lib, self.lib.rt_readback_rgb8(self.ctx, out.ctypes.data))
+        return out
+
+    def readback_f32(self):
+        out = np.zeros((self.H, self.W, 3), np.float32)
+        _check(self.lib, self.lib.rt_readback_f32(self.ctx, out.ctypes.data))
+        return out
+
+    def readback_accum(self):
+        out = np.zeros((self.H, self.W, 4), np.uint64)
+        _check(self.lib, self.lib.rt_readback_accum(self.ctx, out.ctypes.data))
+        return out
+
+    def resolve_device(self):
+        _check(self.lib, self.lib.rt_resolve_device(self.ctx))
+
+    def device_accum(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        _check(self.lib, self.lib.rt_device_accum(self.ctx, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def device_rgb8(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        _check(self.lib, self.lib.rt_device_rgb8(self.ctx, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def render_frame(self, scene, W, H, spp, max_depth=50, seed=1, flags=0, out=None, packed=None):
+        """The cuda_impl()-shaped call: host scene in, host RGB8 out, copies inside."""
+        sph, mat = packed if packed is not None else pack_scene(scene)
+        cam = np.ascontiguousarray(scene.camera, np.float32)
+        if out is None:
+            out = np.zeros((H, W, 3), np.uint8)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), 0, int(flags))
+        _check(self.lib, self.lib.rt_render_frame(self.ctx, sph.ctypes.data, sph.shape[0], mat.ctypes.data, mat.shape[0],
+                                                   cam.ctypes.data_as(C.POINTER(C.c_float)), int(W), int(H), C.byref(p),
+                                                   out.ctypes.data))
+        self.W, self.H = int(W), int(H)
+        return out
+
+    # ---- statistics / probes ------------------------------------------------
+    def stats(self):
+        s = RtStats()
+        _check(self.lib, self.lib.rt_stats_get(self.ctx, C.byref(s)))
+        return s.as_dict()
+
+    def reset_stats(self):
+        _check(self.lib, self.lib.rt_stats_reset(self.ctx))
+
+    def fp32_peak_probe(self):
+        out = (C.c_double * 3)()
+        _check(self.lib, self.lib.rt_fp32_peak_probe(self.ctx, out))
+        return dict(tflops=out[0], ms=out[1], sm_count=int(out[2]))
+
+
+def write_ppm(path, rgb8):
+    lib = load_library()
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    H, W = rgb8.shape[:2]
+    _check(lib, lib.rt_write_ppm(os.fsencode(path), W, H, rgb8.ctypes.data))
+
+
+class TileQueue:
+    """Node-level work counter shared by the ranks of one box (rt_queue_*)."""
+
+    def __init__(self, name: str, create: bool):
+        self.lib = load_library()
+        self.q = C.c_void_p()
+        self.create = create
+        _check(self.lib, self.lib.rt_queue_open(C.byref(self.q), name.encode(), 1 if create else 0))
+
+    def reset(self, value=0):
+        _check(self.lib, self.lib.rt_queue_reset(self.q, int(value)))
+
+    def next(self, n=1) -> int:
+        prev = C.c_uint64()
+        _check(self.lib, self.lib.rt_queue_next(self.q, int(n), C.byref(prev)))
+        return int(prev.value)
+
+    def close(self):
+        if self.q:
+            self.lib.rt_queue_close(self.q, 1 if self.create else 0)
+            self.q = None

@@ -1,0 +1,693 @@
+// rt_api.cu -- the C ABI of include/rt_api.h: context, scene/camera upload, render scheduling,
+// readback, statistics, PPM writer, FP32 probe and the node-level tile queue.
+// Host code only (compiled with -Xcompiler -ffp-contract=off so the camera maths keeps the reference's
+// float rounding); all device work is in rt_kernels_{exact,fast}.cu, rt_common.cu and rt_lbvh.cu.
+#include <atomic>
+#include <cerrno>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include "../../include/rt_api.h"
+#include "rt_common.h"
+#include "rt_lbvh.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string &msg)
+{
+    g_err = msg;
+    return code;
+}
+int cuda_fail(cudaError_t e, const char *what)
+{
+    return fail(RT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+}
+#define CK(call)                                              \
+    do {                                                      \
+        cudaError_t e_ = (call);                              \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);   \
+    } while (0)
+
+struct EventPair { cudaEvent_t a, b; };
+
+}  // namespace
+
+struct rt_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+
+    // scene
+    float4 *d_sph = nullptr; float *d_rad = nullptr; uint32_t *d_meta = nullptr; float4 *d_mat = nullptr;
+    uint32_t n = 0, npad = 0, m = 0;
+    rt_lbvh *bvh = nullptr;
+    bool bvh_valid = false;
+
+    RtDeviceCamera cam{};
+    bool have_cam = false;
+
+    uint32_t W = 0, H = 0;
+    unsigned long long *d_accum = nullptr;
+    unsigned char *d_rgb8 = nullptr;
+    float *d_meanf = nullptr;
+
+    uint32_t *d_counter = nullptr;          // ring of work counters, one per launch
+    uint32_t counter_slot = 0;
+    unsigned long long *d_stats = nullptr;  // 8 x u64
+    float *d_scratch = nullptr;
+
+    void *h_pin = nullptr; size_t h_pin_bytes = 0;   // pinned staging for uploads / readbacks
+
+    std::vector<EventPair> free_events, pending;
+    rt_stats hs{};                          // host-side part of the statistics
+    int occ[2][2] = {{0, 0}, {0, 0}};       // cached CTAs/SM [exact][lbvh]
+    size_t occ_smem[2][2] = {{0, 0}, {0, 0}};
+};
+
+namespace {
+
+const uint32_t kCounterRing = 4096;
+
+int ensure_pinned(rt_ctx *c, size_t bytes)
+{
+    if (bytes <= c->h_pin_bytes) return RT_OK;
+    if (c->h_pin) { cudaFreeHost(c->h_pin); c->h_pin = nullptr; c->h_pin_bytes = 0; }
+    size_t want = bytes + bytes / 4 + 4096;
+    CK(cudaMallocHost(&c->h_pin, want));
+    c->h_pin_bytes = want;
+    return RT_OK;
+}
+
+int drain_events(rt_ctx *c)
+{
+    for (auto &p : c->pending) {
+        CK(cudaEventSynchronize(p.b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, p.a, p.b));
+        c->hs.render_ms += ms;
+        c->hs.last_render_ms = ms;
+        c->free_events.push_back(p);
+    }
+    c->pending.clear();
+    return RT_OK;
+}
+
+int get_events(rt_ctx *c, EventPair *out)
+{
+    if (c->pending.size() > 256) { int r = drain_events(c); if (r) return r; }
+    if (!c->free_events.empty()) { *out = c->free_events.back(); c->free_events.pop_back(); return RT_OK; }
+    CK(cudaEventCreate(&out->a));
+    CK(cudaEventCreate(&out->b));
+    return RT_OK;
+}
+
+void free_scene(rt_ctx *c)
+{
+    cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat);
+    c->d_sph = nullptr; c->d_rad = nullptr; c->d_meta = nullptr; c->d_mat = nullptr;
+    c->n = c->npad = c->m = 0;
+    c->bvh_valid = false;
+}
+
+void free_framebuffer(rt_ctx *c)
+{
+    cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_meanf);
+    c->d_accum = nullptr; c->d_rgb8 = nullptr; c->d_meanf = nullptr;
+    c->W = c->H = 0;
+}
+
+RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
+{
+    RtDeviceScene s{};
+    s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
+    s.n = c->n; s.npad = c->npad;
+    if (lbvh && c->bvh_valid) rt_lbvh_fill(c->bvh, &s);
+    return s;
+}
+
+// brute force unless asked for / forced by size
+int pick_accel(rt_ctx *c, uint32_t flags, bool *lbvh)
+{
+    bool want_bvh = (flags & RT_FLAG_ACCEL_LBVH) != 0;
+    bool want_brute = (flags & RT_FLAG_ACCEL_BRUTE) != 0;
+    if (want_bvh && want_brute) return fail(RT_ERR_INVALID, "both RT_FLAG_ACCEL_BRUTE and RT_FLAG_ACCEL_LBVH set");
+    if (!want_bvh && !want_brute) want_bvh = c->n > RT_BRUTE_MAX_SPHERES;
+    if (!want_bvh && c->n > RT_BRUTE_MAX_SPHERES)
+        return fail(RT_ERR_INVALID, "brute force supports at most RT_BRUTE_MAX_SPHERES spheres (shared-memory staging)");
+    if (want_bvh && !c->bvh_valid) {
+        if (!c->bvh) { int r = rt_lbvh_create(&c->bvh); if (r) return fail(RT_ERR_CUDA, "rt_lbvh_create failed"); }
+        float ms = 0.f; unsigned launches = 0;
+        cudaError_t e = rt_lbvh_build(c->bvh, c->d_sph, c->d_rad, c->n, c->stream, &ms, &launches);
+        if (e != cudaSuccess) return cuda_fail(e, "rt_lbvh_build");
+        c->hs.bvh_build_ms = ms;
+        c->hs.launches += launches;
+        c->bvh_valid = true;
+    }
+    *lbvh = want_bvh;
+    return RT_OK;
+}
+
+int occupancy(rt_ctx *c, bool exact, bool lbvh, size_t smem, int *ctas)
+{
+    int &slot = c->occ[exact][lbvh];
+    if (slot == 0 || c->occ_smem[exact][lbvh] != smem) {
+        int v = 0;
+        cudaError_t e = exact ? rtx::render_occupancy(smem, lbvh, &v) : rtf::render_occupancy(smem, lbvh, &v);
+        if (e != cudaSuccess) return cuda_fail(e, "render_occupancy");
+        if (v < 1) return fail(RT_ERR_INVALID, "render kernel does not fit on an SM (scene too large for shared memory)");
+        slot = v;
+        c->occ_smem[exact][lbvh] = smem;
+    }
+    *ctas = slot;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *rt_last_error(void) { return g_err.c_str(); }
+const char *rt_version(void) { return "rtiow-b200 0.1 (sm_100a)"; }
+
+int rt_create(rt_ctx **out, int device)
+{
+    if (!out) return fail(RT_ERR_INVALID, "rt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(RT_ERR_NO_DEVICE, std::string("no usable CUDA device (") + cudaGetErrorString(e) +
+                                          "); this backend has no CPU fallback");
+    if (device < 0 || device >= count) return fail(RT_ERR_INVALID, "rt_create: device ordinal out of range");
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop{};
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(RT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
+    rt_ctx *c = new (std::nothrow) rt_ctx();
+    if (!c) return fail(RT_ERR_SYS, "out of host memory");
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    CK(cudaMalloc(&c->d_counter, kCounterRing * sizeof(uint32_t)));
+    CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
+    CK(cudaMalloc(&c->d_stats, 8 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(c->d_stats, 0, 8 * sizeof(unsigned long long), c->stream));
+    CK(cudaMalloc(&c->d_scratch, 256));
+    *out = c;
+    return RT_OK;
+}
+
+int rt_destroy(rt_ctx *c)
+{
+    if (!c) return RT_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    free_framebuffer(c);
+    if (c->bvh) rt_lbvh_destroy(c->bvh);
+    cudaFree(c->d_counter); cudaFree(c->d_stats); cudaFree(c->d_scratch);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto &p : c->free_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return RT_OK;
+}
+
+int rt_set_stream(rt_ctx *c, void *cuda_stream)
+{
+    if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return RT_OK;
+}
+
+int rt_sync(rt_ctx *c)
+{
+    if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    return drain_events(c);
+}
+
+int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_material *materials, uint32_t m)
+{
+    if (!c || !spheres || !materials || n == 0 || m == 0) return fail(RT_ERR_INVALID, "rt_scene_upload: empty scene or NULL argument");
+    if (m >= (1u << 30)) return fail(RT_ERR_INVALID, "rt_scene_upload: too many materials");
+    CK(cudaSetDevice(c->device));
+    for (uint32_t i = 0; i < m; ++i)
+        if (materials[i].kind > 2u) return fail(RT_ERR_INVALID, "rt_scene_upload: unknown material kind");
+    for (uint32_t i = 0; i < n; ++i)
+        if (spheres[i].mat >= m) return fail(RT_ERR_INVALID, "rt_scene_upload: sphere references a missing material");
+
+    uint32_t npad = (n + 31u) & ~31u;
+    if (npad != c->npad || m != c->m) {
+        CK(cudaStreamSynchronize(c->stream));
+        free_scene(c);
+        CK(cudaMalloc(&c->d_sph, (size_t)npad * sizeof(float4)));
+        CK(cudaMalloc(&c->d_rad, (size_t)npad * sizeof(float)));
+        CK(cudaMalloc(&c->d_meta, (size_t)npad * sizeof(uint32_t)));
+        CK(cudaMalloc(&c->d_mat, (size_t)m * sizeof(float4)));
+    }
+    size_t b_sph = (size_t)npad * 16, b_rad = (size_t)npad * 4, b_meta = (size_t)npad * 4, b_mat = (size_t)m * 16;
+    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat);
+    if (r) return r;
+    CK(cudaStreamSynchronize(c->stream));   // staging buffer may still be in flight
+    char *h = (char *)c->h_pin;
+    float4 *hs = (float4 *)h;
+    float *hr = (float *)(h + b_sph);
+    uint32_t *hm = (uint32_t *)(h + b_sph + b_rad);
+    float4 *hmat = (float4 *)(h + b_sph + b_rad + b_meta);
+    for (uint32_t i = 0; i < npad; ++i) {
+        if (i < n) {
+            const rt_sphere &s = spheres[i];
+            hs[i] = make_float4(s.cx, s.cy, s.cz, s.r * s.r);   // radius*radius, src/raytracer.hxx:59
+            hr[i] = s.r;
+            hm[i] = s.mat | (materials[s.mat].kind << 30);
+        } else {
+            hs[i] = make_float4(0.f, 0.f, 0.f, -std::numeric_limits<float>::infinity());   // never a candidate
+            hr[i] = 1.f;
+            hm[i] = 0u;
+        }
+    }
+    for (uint32_t i = 0; i < m; ++i) hmat[i] = make_float4(materials[i].r, materials[i].g, materials[i].b, materials[i].param);
+    CK(cudaMemcpyAsync(c->d_sph, hs, b_sph, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_rad, hr, b_rad, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_meta, hm, b_meta, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_mat, hmat, b_mat, cudaMemcpyHostToDevice, c->stream));
+    c->n = n; c->npad = npad; c->m = m;
+    c->bvh_valid = false;
+    return RT_OK;
+}
+
+// src/camera.hxx:24-44, float arithmetic in the same order (this TU is built with -ffp-contract=off).
+int rt_camera_set(rt_ctx *c, const float pos[3], const float lookat[3], const float up[3],
+                  float aspect, float vfov_deg, float aperture, float focus_dist)
+{
+    if (!c || !pos || !lookat || !up) return fail(RT_ERR_INVALID, "rt_camera_set: NULL argument");
+    struct v3 { float x, y, z; };
+    auto sub = [](v3 a, v3 b) { return v3{a.x - b.x, a.y - b.y, a.z - b.z}; };
+    auto add = [](v3 a, v3 b) { return v3{a.x + b.x, a.y + b.y, a.z + b.z}; };
+    auto muls = [](v3 a, float s) { return v3{a.x * s, a.y * s, a.z * s}; };
+    auto cross = [](v3 a, v3 b) { return v3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
+    auto normalize = [](v3 a) {
+        float len = std::sqrt(a.x * a.x + a.y * a.y + a.z * a.z);
+        if (std::fabs(len) > FLT_MIN) { a.x /= len; a.y /= len; a.z /= len; }
+        return a;
+    };
+    v3 position{pos[0], pos[1], pos[2]}, look{lookat[0], lookat[1], lookat[2]}, upv{up[0], up[1], up[2]};
+    float theta = (vfov_deg * static_cast<float>(0.01745329251994329576923690768489)) / 2.f;
+    float height = std::tan(theta);
+    float width = height * aspect;
+    v3 w = normalize(sub(position, look));
+    v3 u = normalize(cross(upv, w));
+    v3 v = normalize(cross(w, u));
+    v3 llc = sub(position, muls(add(add(muls(u, width), muls(v, height)), w), focus_dist));
+    v3 hor = muls(muls(muls(u, width), focus_dist), 2.f);
+    v3 ver = muls(muls(muls(v, height), focus_dist), 2.f);
+    RtDeviceCamera &d = c->cam;
+    d.ox = position.x; d.oy = position.y; d.oz = position.z;
+    d.llx = llc.x; d.lly = llc.y; d.llz = llc.z;
+    d.hx = hor.x; d.hy = hor.y; d.hz = hor.z;
+    d.vx = ver.x; d.vy = ver.y; d.vz = ver.z;
+    d.lens_radius = aperture / 2.f;
+    c->have_cam = true;
+    return RT_OK;
+}
+
+int rt_camera_get(rt_ctx *c, float out[13])
+{
+    if (!c || !out || !c->have_cam) return fail(RT_ERR_INVALID, "rt_camera_get: no camera set");
+    const RtDeviceCamera &d = c->cam;
+    const float v[13] = {d.ox, d.oy, d.oz, d.llx, d.lly, d.llz, d.hx, d.hy, d.hz, d.vx, d.vy, d.vz, d.lens_radius};
+    std::memcpy(out, v, sizeof v);
+    return RT_OK;
+}
+
+int rt_framebuffer(rt_ctx *c, uint32_t width, uint32_t height)
+{
+    if (!c || width == 0 || height == 0) return fail(RT_ERR_INVALID, "rt_framebuffer: zero size");
+    if ((unsigned long long)width * height >= (1ull << 31)) return fail(RT_ERR_INVALID, "rt_framebuffer: image too large");
+    CK(cudaSetDevice(c->device));
+    if (width != c->W || height != c->H) {
+        CK(cudaStreamSynchronize(c->stream));
+        free_framebuffer(c);
+        size_t npix = (size_t)width * height;
+        CK(cudaMalloc(&c->d_accum, npix * 4 * sizeof(unsigned long long)));
+        CK(cudaMalloc(&c->d_rgb8, npix * 3 + 16));
+        CK(cudaMalloc(&c->d_meanf, npix * 3 * sizeof(float) + 64));
+        c->W = width; c->H = height;
+    }
+    return rt_clear(c);
+}
+
+int rt_clear(rt_ctx *c)
+{
+    if (!c || !c->d_accum) return fail(RT_ERR_INVALID, "rt_clear: no framebuffer");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemsetAsync(c->d_accum, 0, (size_t)c->W * c->H * 4 * sizeof(unsigned long long), c->stream));
+    return RT_OK;
+}
+
+int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
+{
+    if (!c || !tile || !p) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
+    if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_render: no scene uploaded");
+    if (!c->have_cam) return fail(RT_ERR_INVALID, "rt_render: no camera set");
+    if (!c->d_accum) return fail(RT_ERR_INVALID, "rt_render: no framebuffer");
+    if (p->max_depth == 0) return fail(RT_ERR_INVALID, "rt_render: max_depth must be >= 1");
+    if (tile->w == 0 || tile->h == 0 || p->spp == 0) return RT_OK;   // empty tile / zero samples: nothing to add
+    if ((unsigned long long)tile->x0 + tile->w > c->W || (unsigned long long)tile->y0 + tile->h > c->H)
+        return fail(RT_ERR_INVALID, "rt_render: tile outside the framebuffer");
+    if ((unsigned long long)p->sample_base + p->spp > 0xffffffffull) return fail(RT_ERR_INVALID, "rt_render: sample index overflow");
+    CK(cudaSetDevice(c->device));
+
+    const bool exact = (p->flags & RT_FLAG_EXACT) != 0;
+    bool lbvh = false;
+    int r = pick_accel(c, p->flags, &lbvh);
+    if (r) return r;
+    size_t smem = rt_render_smem_bytes(c->npad, lbvh);
+    int ctas = 0;
+    r = occupancy(c, exact, lbvh, smem, &ctas);
+    if (r) return r;
+
+    EventPair ev;
+    r = get_events(c, &ev);
+    if (r) return r;
+    CK(cudaEventRecord(ev.a, c->stream));
+
+    CK(rt_launch_add_count(c->d_accum, c->W, tile->x0, tile->y0, tile->w, tile->h, p->spp, c->stream));
+    c->hs.launches += 1;
+
+    RtRenderArgs a{};
+    a.sc = device_scene(c, lbvh);
+    a.cam = c->cam;
+    a.accum = c->d_accum;
+    a.W = c->W; a.H = c->H;
+    a.x0 = tile->x0; a.y0 = tile->y0; a.w = tile->w; a.h = tile->h;
+    a.spp = p->spp; a.depth = p->max_depth; a.sample_base = p->sample_base;
+    a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
+    a.stats = c->d_stats;
+
+    // bands of tile pixels so that items = P * spp stays below 2^31 (32-bit item arithmetic in the kernel)
+    const unsigned long long npx = (unsigned long long)tile->w * tile->h;
+    unsigned long long P = npx;
+    if (npx * p->spp >= (1ull << 31)) P = ((1ull << 31) - 1) / p->spp;
+    if (P == 0) return fail(RT_ERR_INVALID, "rt_render: spp too large");
+    for (unsigned long long p0 = 0; p0 < npx; p0 += P) {
+        a.p0 = (uint32_t)p0;
+        a.P = (uint32_t)((npx - p0 < P) ? (npx - p0) : P);
+        a.total_items = a.P * p->spp;
+        if (c->counter_slot == kCounterRing) {
+            CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
+            c->counter_slot = 0;
+        }
+        a.work_counter = c->d_counter + c->counter_slot++;
+        unsigned long long want_ctas = (a.total_items + (unsigned long long)RT_THREADS * RT_RPT - 1) / ((unsigned long long)RT_THREADS * RT_RPT);
+        int grid = c->sm_count * ctas;
+        if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
+        if (grid < 1) grid = 1;
+        cudaError_t e = exact ? rtx::launch_render(a, grid, smem, c->stream, lbvh)
+                              : rtf::launch_render(a, grid, smem, c->stream, lbvh);
+        if (e != cudaSuccess) return cuda_fail(e, "launch_render");
+        c->hs.launches += 1;
+    }
+    CK(cudaEventRecord(ev.b, c->stream));
+    c->pending.push_back(ev);
+    return RT_OK;
+}
+
+static int hits_common(rt_ctx *c, RtHitArgs &a, unsigned long long total, uint32_t flags,
+                       int32_t *sphere_index, float *t, float *normal_xyz)
+{
+    const bool exact = (flags & RT_FLAG_EXACT) != 0;
+    bool lbvh = false;
+    int r = pick_accel(c, flags, &lbvh);
+    if (r) return r;
+    int32_t *d_idx = nullptr; float *d_t = nullptr, *d_n = nullptr;
+    CK(cudaMalloc(&d_idx, total * 4));
+    CK(cudaMalloc(&d_t, total * 4));
+    CK(cudaMalloc(&d_n, total * 12));
+    a.sc = device_scene(c, lbvh);
+    a.idx = d_idx; a.t = d_t; a.normal = d_n;
+    a.stats = c->d_stats;
+    cudaError_t e = exact ? rtx::launch_hits(a, c->stream, lbvh) : rtf::launch_hits(a, c->stream, lbvh);
+    int rc = RT_OK;
+    if (e != cudaSuccess) rc = cuda_fail(e, "launch_hits");
+    c->hs.launches += 1;
+    if (!rc) {
+        cudaError_t e1 = cudaMemcpyAsync(sphere_index, d_idx, total * 4, cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e2 = cudaMemcpyAsync(t, d_t, total * 4, cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e3 = cudaMemcpyAsync(normal_xyz, d_n, total * 12, cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e4 = cudaStreamSynchronize(c->stream);
+        if (e1 != cudaSuccess) rc = cuda_fail(e1, "D2H idx");
+        else if (e2 != cudaSuccess) rc = cuda_fail(e2, "D2H t");
+        else if (e3 != cudaSuccess) rc = cuda_fail(e3, "D2H normal");
+        else if (e4 != cudaSuccess) rc = cuda_fail(e4, "sync");
+    }
+    cudaFree(d_idx); cudaFree(d_t); cudaFree(d_n);
+    return rc;
+}
+
+int rt_primary_hits(rt_ctx *c, const rt_tile *tile, uint32_t flags, int32_t *sphere_index, float *t, float *normal_xyz)
+{
+    if (!c || !tile || !sphere_index || !t || !normal_xyz) return fail(RT_ERR_INVALID, "rt_primary_hits: NULL argument");
+    if (!c->d_sph || !c->have_cam) return fail(RT_ERR_INVALID, "rt_primary_hits: scene and camera must be set");
+    if (c->W == 0) return fail(RT_ERR_INVALID, "rt_primary_hits: call rt_framebuffer first (it defines W x H)");
+    if (tile->w == 0 || tile->h == 0) return RT_OK;
+    if ((unsigned long long)tile->x0 + tile->w > c->W || (unsigned long long)tile->y0 + tile->h > c->H)
+        return fail(RT_ERR_INVALID, "rt_primary_hits: tile outside the framebuffer");
+    CK(cudaSetDevice(c->device));
+    RtHitArgs a{};
+    a.cam = c->cam;
+    a.W = c->W; a.H = c->H; a.x0 = tile->x0; a.y0 = tile->y0; a.w = tile->w; a.h = tile->h;
+    a.rays = nullptr; a.nrays = 0;
+    return hits_common(c, a, (unsigned long long)tile->w * tile->h, flags, sphere_index, t, normal_xyz);
+}
+
+int rt_closest_hits(rt_ctx *c, const float *rays6, uint64_t n, uint32_t flags, int32_t *sphere_index, float *t, float *normal_xyz)
+{
+    if (!c || !sphere_index || !t || !normal_xyz) return fail(RT_ERR_INVALID, "rt_closest_hits: NULL argument");
+    if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_closest_hits: no scene uploaded");
+    if (n == 0) return RT_OK;
+    if (!rays6) return fail(RT_ERR_INVALID, "rt_closest_hits: rays is NULL");
+    CK(cudaSetDevice(c->device));
+    float *d_rays = nullptr;
+    CK(cudaMalloc(&d_rays, n * 24));
+    cudaError_t e = cudaMemcpyAsync(d_rays, rays6, n * 24, cudaMemcpyHostToDevice, c->stream);
+    if (e != cudaSuccess) { cudaFree(d_rays); return cuda_fail(e, "H2D rays"); }
+    RtHitArgs a{};
+    a.rays = d_rays; a.nrays = n;
+    int rc = hits_common(c, a, n, flags, sphere_index, t, normal_xyz);
+    cudaFree(d_rays);
+    return rc;
+}
+
+int rt_resolve_device(rt_ctx *c)
+{
+    if (!c || !c->d_accum) return fail(RT_ERR_INVALID, "rt_resolve_device: no framebuffer");
+    CK(cudaSetDevice(c->device));
+    CK(rt_launch_resolve(c->d_accum, (unsigned long long)c->W * c->H, c->d_rgb8, c->d_meanf, c->stream));
+    c->hs.launches += 1;
+    return RT_OK;
+}
+
+int rt_readback_rgb8(rt_ctx *c, uint8_t *dst)
+{
+    if (!c || !dst) return fail(RT_ERR_INVALID, "rt_readback_rgb8: NULL argument");
+    int r = rt_resolve_device(c);
+    if (r) return r;
+    size_t bytes = (size_t)c->W * c->H * 3;
+    r = ensure_pinned(c, bytes);
+    if (r) return r;
+    CK(cudaMemcpyAsync(c->h_pin, c->d_rgb8, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    std::memcpy(dst, c->h_pin, bytes);
+    return drain_events(c);
+}
+
+int rt_readback_f32(rt_ctx *c, float *dst)
+{
+    if (!c || !dst) return fail(RT_ERR_INVALID, "rt_readback_f32: NULL argument");
+    int r = rt_resolve_device(c);
+    if (r) return r;
+    CK(cudaMemcpyAsync(dst, c->d_meanf, (size_t)c->W * c->H * 12, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return drain_events(c);
+}
+
+int rt_readback_accum(rt_ctx *c, uint64_t *dst)
+{
+    if (!c || !dst || !c->d_accum) return fail(RT_ERR_INVALID, "rt_readback_accum: NULL argument or no framebuffer");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst, c->d_accum, (size_t)c->W * c->H * 32, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return drain_events(c);
+}
+
+int rt_device_accum(rt_ctx *c, void **dptr, size_t *bytes)
+{
+    if (!c || !dptr || !c->d_accum) return fail(RT_ERR_INVALID, "rt_device_accum: no framebuffer");
+    *dptr = c->d_accum;
+    if (bytes) *bytes = (size_t)c->W * c->H * 32;
+    return RT_OK;
+}
+
+int rt_device_rgb8(rt_ctx *c, void **dptr, size_t *bytes)
+{
+    if (!c || !dptr || !c->d_rgb8) return fail(RT_ERR_INVALID, "rt_device_rgb8: no framebuffer");
+    *dptr = c->d_rgb8;
+    if (bytes) *bytes = (size_t)c->W * c->H * 3;
+    return RT_OK;
+}
+
+int rt_render_frame(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_material *materials, uint32_t m,
+                    const float cam[13], uint32_t width, uint32_t height, const rt_render_params *params, uint8_t *rgb8_out)
+{
+    if (!c || !cam || !params || !rgb8_out) return fail(RT_ERR_INVALID, "rt_render_frame: NULL argument");
+    int r = rt_scene_upload(c, spheres, n, materials, m);
+    if (r) return r;
+    r = rt_camera_set(c, cam, cam + 3, cam + 6, cam[9], cam[10], cam[11], cam[12]);
+    if (r) return r;
+    r = rt_framebuffer(c, width, height);
+    if (r) return r;
+    rt_tile full = {0, 0, width, height};
+    r = rt_render(c, &full, params);
+    if (r) return r;
+    return rt_readback_rgb8(c, rgb8_out);
+}
+
+int rt_stats_get(rt_ctx *c, rt_stats *out)
+{
+    if (!c || !out) return fail(RT_ERR_INVALID, "rt_stats_get: NULL argument");
+    int r = rt_sync(c);
+    if (r) return r;
+    unsigned long long h[8];
+    CK(cudaMemcpy(h, c->d_stats, sizeof h, cudaMemcpyDeviceToHost));
+    *out = c->hs;
+    out->samples = h[0]; out->segments = h[1]; out->sky = h[2]; out->absorbed = h[3]; out->capped = h[4];
+    out->node_visits = h[5];
+    out->sphere_tests = h[6];
+    return RT_OK;
+}
+
+int rt_stats_reset(rt_ctx *c)
+{
+    if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
+    int r = rt_sync(c);
+    if (r) return r;
+    CK(cudaMemsetAsync(c->d_stats, 0, 8 * sizeof(unsigned long long), c->stream));
+    c->hs = rt_stats{};
+    return RT_OK;
+}
+
+// src/main.cxx:87-101: "P6\n" W " " H "\n255\n" then the raw texels.
+int rt_write_ppm(const char *path, uint32_t width, uint32_t height, const uint8_t *rgb8)
+{
+    if (!path || !rgb8) return fail(RT_ERR_INVALID, "rt_write_ppm: NULL argument");
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(RT_ERR_IO, std::string("bad file: ") + path);
+    std::fprintf(f, "P6\n%u %u\n255\n", width, height);
+    size_t bytes = (size_t)width * height * 3;
+    size_t w = std::fwrite(rgb8, 1, bytes, f);
+    int rc = std::fclose(f);
+    if (w != bytes || rc != 0) return fail(RT_ERR_IO, std::string("short write: ") + path);
+    return RT_OK;
+}
+
+int rt_fp32_peak_probe(rt_ctx *c, double out[3])
+{
+    if (!c || !out) return fail(RT_ERR_INVALID, "rt_fp32_peak_probe: NULL argument");
+    CK(cudaSetDevice(c->device));
+    const int blocks = c->sm_count * 8, iters = 4096;
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    CK(rt_launch_fp32_probe(c->d_scratch, blocks, 256, c->stream));   // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CK(cudaEventRecord(a, c->stream));
+        CK(rt_launch_fp32_probe(c->d_scratch, blocks, iters, c->stream));
+        CK(cudaEventRecord(b, c->stream));
+        CK(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        if (ms < best) best = ms;
+    }
+    c->hs.launches += 6;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    double flop = (double)blocks * 256.0 * iters * 64.0 * 2.0;
+    out[0] = flop / (best * 1e-3) * 1e-12;
+    out[1] = best;
+    out[2] = c->sm_count;
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------- node-level tile queue (POSIX shm)
+struct rt_queue {
+    std::atomic<uint64_t> *ctr;
+    std::string name;
+    int fd;
+};
+
+int rt_queue_open(rt_queue **out, const char *name, int create)
+{
+    if (!out || !name || name[0] != '/') return fail(RT_ERR_INVALID, "rt_queue_open: name must start with '/'");
+    static_assert(sizeof(std::atomic<uint64_t>) == 8, "lock-free 64-bit atomic expected");
+    int fd = shm_open(name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
+    if (fd < 0) return fail(RT_ERR_SYS, std::string("shm_open(") + name + "): " + std::strerror(errno));
+    if (create && ftruncate(fd, 4096) != 0) { int e = errno; close(fd); return fail(RT_ERR_SYS, std::string("ftruncate: ") + std::strerror(e)); }
+    void *p = mmap(nullptr, 4096, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (p == MAP_FAILED) { int e = errno; close(fd); return fail(RT_ERR_SYS, std::string("mmap: ") + std::strerror(e)); }
+    rt_queue *q = new (std::nothrow) rt_queue();
+    if (!q) { munmap(p, 4096); close(fd); return fail(RT_ERR_SYS, "out of host memory"); }
+    q->ctr = reinterpret_cast<std::atomic<uint64_t> *>(p);
+    q->name = name;
+    q->fd = fd;
+    if (create) q->ctr->store(0, std::memory_order_seq_cst);
+    *out = q;
+    return RT_OK;
+}
+
+int rt_queue_reset(rt_queue *q, uint64_t value)
+{
+    if (!q) return fail(RT_ERR_INVALID, "queue is NULL");
+    q->ctr->store(value, std::memory_order_seq_cst);
+    return RT_OK;
+}
+
+int rt_queue_next(rt_queue *q, uint64_t n, uint64_t *previous)
+{
+    if (!q || !previous) return fail(RT_ERR_INVALID, "rt_queue_next: NULL argument");
+    *previous = q->ctr->fetch_add(n, std::memory_order_seq_cst);
+    return RT_OK;
+}
+
+int rt_queue_close(rt_queue *q, int unlink_name)
+{
+    if (!q) return RT_OK;
+    munmap((void *)q->ctr, 4096);
+    close(q->fd);
+    if (unlink_name) shm_unlink(q->name.c_str());
+    delete q;
+    return RT_OK;
+}
+
+}  // extern "C"

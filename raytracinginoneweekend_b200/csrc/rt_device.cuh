@@ -1,0 +1,543 @@
+// rt_device.cuh -- device code of the path-tracing hot path, compiled TWICE:
+//   rt_kernels_exact.cu : -DRT_EXACT=1, nvcc --fmad=false  -> namespace rtx.  Every float operation is an
+//                         IEEE mul/add/div/sqrt in the reference's operation order; results are bit-identical
+//                         to the CPU oracle (oracle/rt_oracle.c) path by path.
+//   rt_kernels_fast.cu  : -DRT_EXACT=0, FMA contraction on  -> namespace rtf.  Same algorithm, fused
+//                         multiply-adds in the sphere loop; this is the throughput path.
+//
+// Reference semantics restated here (paths relative to the reference repo):
+//   intersect            src/raytracer.hxx:52-92      hit_world (first minimum)   src/raytracer.hxx:94-118
+//   apply_material       src/raytracer.hxx:120-199    schlick (double)            src/raytracer.hxx:45-50
+//   random_in_unit_sphere src/raytracer.hxx:32-43     camera::ray                 src/camera.hxx:46-57
+//   app::color           src/main.cxx:52-75           background                  src/main.cxx:47-50,71
+//   reflect/refract/normalize/mix                     src/math.hxx:219-227,294-335
+#pragma once
+#include <cfloat>
+#include "rt_types.h"
+
+#ifndef RT_EXACT
+#error "define RT_EXACT to 0 or 1"
+#endif
+
+#if RT_EXACT
+#define RT_NS rtx
+#else
+#define RT_NS rtf
+#endif
+
+namespace RT_NS {
+
+#define RT_FULL 0xffffffffu
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+
+// ------------------------------------------------------------------ PTX helpers (TMA bulk copy)
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "RT_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra RT_DONE;\n"
+        "bra RT_WAIT;\n"
+        "RT_DONE:\n"
+        "}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+
+// Stage the SoA sphere records {cx,cy,cz,r*r} into shared memory with one TMA bulk copy per <=64 KB
+// piece; every thread waits on the mbarrier.  Called once per CTA (the render kernel is persistent).
+__device__ __forceinline__ void stage_spheres(float4 *s_sph, const float4 *g_sph, uint32_t npad, uint64_t *bar)
+{
+    if (threadIdx.x == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t bytes = npad * 16u;
+        mbar_expect_tx(bar, bytes);
+        for (uint32_t off = 0; off < bytes; off += 65536u) {
+            uint32_t piece = min(65536u, bytes - off);
+            tma_bulk_g2s((char *)s_sph + off, (const char *)g_sph + off, piece, bar);
+        }
+    }
+    mbar_wait(bar, 0);
+}
+
+// ------------------------------------------------------------------ RNG: Philox4x32-10, counter based
+// counter = (pixel, sample, event, block), key = seed.  event 0 = camera ray (block 0 words 0,1 = pixel
+// jitter; lens-ball attempts start at block 1), event b+1 = the scatter after segment b (ball attempts
+// start at block 0, attempt k uses words 0..2 of block k; the dielectric uses word 0 of block 0).
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1)
+{
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f; }
+__device__ __forceinline__ float s11(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f * 2.f + -1.f; }
+
+// ------------------------------------------------------------------ vector math in the reference's order
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// src/math.hxx:219-227
+__device__ __forceinline__ f3 normalize3(f3 a)
+{
+    float len = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
+    if (fabsf(len) > FLT_MIN) { a.x = a.x / len; a.y = a.y / len; a.z = a.z / len; }
+    return a;
+}
+// src/math.hxx:294-298
+__device__ __forceinline__ f3 reflect3(f3 I, f3 N)
+{
+    float dn = dot3(N, I);
+    return mk3(I.x - (N.x * dn) * 2.f, I.y - (N.y * dn) * 2.f, I.z - (N.z * dn) * 2.f);
+}
+// src/math.hxx:300-309 with its quirk: dot*eta is added to every component; k < 0 gives NaN.
+__device__ __forceinline__ f3 refract3(f3 I, f3 N, float eta)
+{
+    float dv = dot3(N, I);
+    float k = 1.f - eta * eta * (1.f - dv * dv);
+    float sk = sqrtf(k);
+    float s = dv * eta;
+    float z = (k >= 0.f) ? 1.f : 0.f;
+    return mk3((I.x * eta - (N.x * sk + s)) * z, (I.y * eta - (N.y * sk + s)) * z, (I.z * eta - (N.z * sk + s)) * z);
+}
+// src/raytracer.hxx:45-50
+__device__ __forceinline__ float schlick(float ri, float cosine)
+{
+#if RT_EXACT
+    double q = (double)((1.f - ri) / (1.f + ri));
+    double r0 = q * q;
+    double x = (double)(1.f - cosine);
+    double x2 = x * x;
+    double x5 = x2 * x2 * x;
+    return (float)(r0 + (1. - r0) * x5);
+#else
+    float q = (1.f - ri) / (1.f + ri);
+    float r0 = q * q;
+    float x = 1.f - cosine;
+    float x2 = x * x;
+    return r0 + (1.f - r0) * (x2 * x2 * x);
+#endif
+}
+
+// ------------------------------------------------------------------ closest hit, brute force
+// One sphere test: the arithmetic of src/raytracer.hxx:55-61.  In the fast TU the dot products are
+// explicit FMA chains (11 FP32 instructions instead of 18).
+__device__ __forceinline__ float sphere_disc(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
+                                             float a, float &b)
+{
+    float ocx = ox - s.x, ocy = oy - s.y, ocz = oz - s.z;
+#if RT_EXACT
+    b = ocx * dx + ocy * dy + ocz * dz;
+    float c = (ocx * ocx + ocy * ocy + ocz * ocz) - s.w;
+    return b * b - a * c;
+#else
+    b = fmaf(ocz, dz, fmaf(ocy, dy, ocx * dx));
+    float c = fmaf(ocz, ocz, fmaf(ocy, ocy, fmaf(ocx, ocx, -s.w)));
+    return fmaf(b, b, -(a * c));
+#endif
+}
+
+// Exact per-candidate test (src/raytracer.hxx:63-89) against the running closest hit.  Candidates are
+// visited in increasing sphere index and the comparison is strict, so ties keep the LOWEST index --
+// hit_world's stable_partition + first min_element (src/raytracer.hxx:107-117).
+__device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz,
+                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i)
+{
+    float b;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
+    if (disc > 0.f) {
+        float sq = sqrtf(disc);
+        float t = (-b - sq) / a;
+        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        else {
+            t = (-b + sq) / a;
+            if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        }
+    }
+}
+
+// Brute-force closest hit for R rays per thread over the shared-memory sphere buffer.
+// Pass 1 (hot): per sphere 1 LDS.128 (warp-broadcast) + per ray the discriminant and one funnel shift
+//   that pushes its sign bit into a 32-sphere mask word -- no branch, no sqrt, no divide.
+// Pass 2: each lane walks its own candidate bits (typically 3-10 of 488 spheres) and runs the exact
+//   reference test.  Lanes skip empty mask words independently, so the warp iterates max-over-lanes
+//   of the candidate COUNT, not the number of mask words.
+// s_mask layout: [word][ray][thread] (conflict-free).
+template <int R>
+__device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_sph, uint32_t n, uint32_t npad,
+                                                  uint32_t *__restrict__ s_mask, const bool (&live)[R],
+                                                  const float (&ox)[R], const float (&oy)[R], const float (&oz)[R],
+                                                  const float (&dx)[R], const float (&dy)[R], const float (&dz)[R],
+                                                  float (&best_t)[R], int (&best_i)[R])
+{
+    float a[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        a[r] = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+        best_t[r] = FLT_MAX;
+        best_i[r] = -1;
+    }
+    const uint32_t nthreads = blockDim.x;
+    for (uint32_t chunk = 0; chunk < npad; chunk += 32u * RT_CHUNK_WORDS) {
+        const uint32_t nwords = min((uint32_t)RT_CHUNK_WORDS, (npad - chunk) >> 5);
+        for (uint32_t w = 0; w < nwords; ++w) {
+            uint32_t m[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) m[r] = 0u;
+            const float4 *sp = s_sph + chunk + (w << 5);
+#pragma unroll 16
+            for (int k = 0; k < 32; ++k) {
+                float4 s = sp[k];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float b;
+                    float disc = sphere_disc(s, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a[r], b);
+                    // sign bit clear (disc >= +0 or NaN) -> candidate; bit (31-k) of the finished word
+                    m[r] = __funnelshift_l(__float_as_uint(disc), m[r], 1);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) s_mask[(w * R + r) * nthreads + threadIdx.x] = ~m[r];
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            uint32_t w = 0, cand = 0;
+            const uint32_t lim = live[r] ? nwords : 0u;
+            for (;;) {
+                while (cand == 0u && w < lim) { cand = s_mask[(w * R + r) * nthreads + threadIdx.x]; ++w; }
+                if (cand == 0u) break;
+                int bit = __clz(cand);
+                cand &= ~(0x80000000u >> bit);
+                uint32_t j = chunk + ((w - 1u) << 5) + (uint32_t)bit;
+                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a[r], best_t[r], best_i[r]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ warp work pool
+// A warp takes RT_BATCH consecutive work items (pixel, sample) with one atomic and deals them to the
+// lanes whose path ended, by ballot + popc prefix -- terminated paths are replaced immediately, so every
+// lane carries a live ray into the next sphere loop (compaction by regeneration).
+struct WarpPool { uint32_t next, end; bool exhausted; };
+
+__device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, uint32_t *counter, uint32_t total)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t item = 0xffffffffu;
+    uint32_t need = __ballot_sync(RT_FULL, want);
+    while (need) {
+        if (p.next >= p.end) {
+            if (p.exhausted) break;
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(counter, RT_BATCH);
+            base = __shfl_sync(RT_FULL, base, 0);
+            if (base >= total) { p.exhausted = true; break; }
+            p.next = base;
+            p.end = min(base + RT_BATCH, total);
+        }
+        uint32_t avail = p.end - p.next;
+        bool mine = want && item == 0xffffffffu;
+        uint32_t rank = __popc(need & lt);
+        if (mine && rank < avail) item = p.next + rank;
+        p.next += min((uint32_t)__popc(need), avail);
+        need = __ballot_sync(RT_FULL, want && item == 0xffffffffu);
+    }
+    return item;
+}
+
+// ------------------------------------------------------------------ the persistent render kernel
+enum { ST_EMPTY = 0, ST_ACTIVE = 1, ST_DEAD = 2 };
+enum { RM_NONE = 0, RM_UNIFORM = 1, RM_BALL = 2, RM_CAMERA = 3 };
+
+struct PathSlot {
+    float ox, oy, oz, dx, dy, dz;   // current ray (direction NOT normalised, as in the reference)
+    float ar, ag, ab;               // attenuation
+    uint32_t pix, smp, bounce;      // global pixel index (y*W+x), sample index, segments traced so far
+    int st;
+};
+
+struct ThreadStats { uint32_t samples, segments, sky, absorbed, capped; };
+
+__device__ __forceinline__ unsigned long long to_fixed(float c)
+{
+    return (c > 0.f) ? __float2ull_rn(c * RT_FIXED_ONE) : 0ull;
+}
+
+// One shading pass for one path slot: finish the segment just traced (background / material), hand a new
+// camera sample to the slot if its path ended, draw the random numbers every lane needs in ONE shared
+// Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
+__device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
+                                           float best_t, int best_i, WarpPool &pool, ThreadStats &ts)
+{
+    const RtDeviceScene &sc = A.sc;
+    bool want = (S.st != ST_ACTIVE);
+    int mode = RM_NONE;
+    int kind = -1;
+    f3 p = mk3(0, 0, 0), n = mk3(0, 0, 0), unit = mk3(0, 0, 0), refl = mk3(0, 0, 0), refr = mk3(0, 0, 0);
+    float4 m = make_float4(0, 0, 0, 0);
+    float prob = 1.f;
+
+    if (S.st == ST_ACTIVE) {
+        ++ts.segments;
+        unit = normalize3(mk3(S.dx, S.dy, S.dz));                        // ray::unit_direction, src/math.hxx:351
+        if (best_i < 0) {                                                // miss: src/main.cxx:71 (quirk F6: + 1.f)
+            float t = .5f * unit.y + 1.f;
+            float omt = 1.f - t;
+            float cr = (omt + .5f * t) * S.ar, cg = (omt + .7f * t) * S.ag, cb = (omt + 1.f * t) * S.ab;
+            unsigned long long *px = A.accum + 4ull * S.pix;
+            atomicAdd(px + 0, to_fixed(cr));
+            atomicAdd(px + 1, to_fixed(cg));
+            atomicAdd(px + 2, to_fixed(cb));
+            ++ts.sky;
+            want = true;
+        } else if (S.bounce + 1u >= A.depth) {                           // depth exhausted -> black, src/main.cxx:74
+            ++ts.capped;
+            want = true;
+        } else {
+            float4 s = s_sph[best_i];
+            float rad = __ldg(sc.sph_rad + best_i);
+            uint32_t meta = __ldg(sc.sph_meta + best_i);
+            m = __ldg(sc.mat + (meta & 0x3fffffffu));
+            kind = (int)(meta >> 30);
+            p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
+            n = mk3((p.x - s.x) / rad, (p.y - s.y) / rad, (p.z - s.z) / rad);            // src/raytracer.hxx:70
+            if (kind == 0) mode = RM_BALL;
+            else if (kind == 1) { refl = reflect3(unit, n); mode = RM_BALL; }
+            else {                                                        // dielectric, src/raytracer.hxx:158-178
+                f3 outward = mk3(-n.x, -n.y, -n.z);
+                float ri = m.w;
+                float cosine = dot3(unit, n);
+                if (cosine <= 0.f) {
+                    outward = mk3(outward.x * -1.f, outward.y * -1.f, outward.z * -1.f);
+                    ri = 1.f / ri;
+                    cosine = cosine * -1.f;
+                }
+                refr = refract3(unit, outward, ri);
+                if (refr.x * refr.x + refr.y * refr.y + refr.z * refr.z > 0.f) prob = schlick(ri, cosine);
+                refl = reflect3(unit, n);
+                mode = RM_UNIFORM;
+            }
+        }
+    }
+
+    // ---- regeneration: give every ended path a new (pixel, sample)
+    uint32_t item = pool_take(pool, want, A.work_counter, A.total_items);
+    uint32_t px = 0, py = 0;
+    uint32_t ev = S.bounce + 1u;
+    if (want) {
+        if (item != 0xffffffffu) {
+            uint32_t s_i = item / A.P;
+            uint32_t q = A.p0 + (item - s_i * A.P);
+            uint32_t ty = q / A.w;
+            px = A.x0 + (q - ty * A.w);
+            py = A.y0 + ty;
+            S.pix = py * A.W + px;
+            S.smp = A.sample_base + s_i;
+            S.bounce = 0;
+            S.ar = S.ag = S.ab = 1.f;
+            S.st = ST_ACTIVE;
+            ev = 0;
+            mode = RM_CAMERA;
+            ++ts.samples;
+        } else {
+            S.st = ST_EMPTY;
+        }
+    }
+
+    // ---- one Philox loop serves camera jitter, lens / lambert / metal ball samples and the dielectric coin
+    float r0 = 0.f, r1 = 0.f, r2 = 0.f, ju = 0.f, jv = 0.f;
+    const bool camera_lane = (mode == RM_CAMERA);
+    uint32_t blk = 0;
+    while (mode != RM_NONE) {
+        uint4 w = philox4x32_10(S.pix, S.smp, ev, blk, A.key0, A.key1);
+        if (mode == RM_CAMERA) {
+            ju = u01(w.x); jv = u01(w.y);
+            blk = 1;
+            mode = (A.cam.lens_radius != 0.f) ? RM_BALL : RM_NONE;
+        } else if (mode == RM_UNIFORM) {
+            r0 = u01(w.x);
+            mode = RM_NONE;
+        } else {                                                          // src/raytracer.hxx:32-43
+            r0 = s11(w.x); r1 = s11(w.y); r2 = s11(w.z);
+#if RT_EXACT
+            bool reject = sqrtf(r0 * r0 + r1 * r1 + r2 * r2) > 1.f;
+#else
+            bool reject = (r0 * r0 + r1 * r1 + r2 * r2) > 1.f;
+#endif
+            if (reject) ++blk; else mode = RM_NONE;
+        }
+    }
+
+    // ---- next ray
+    if (camera_lane) {                                                    // src/main.cxx:192-200, src/camera.hxx:46-57
+        const RtDeviceCamera &c = A.cam;
+        float u = (float)px / (float)A.W + ju / (float)A.W;
+        float v = (float)py / (float)A.H + jv / (float)A.H;
+        float rdx = r0 * c.lens_radius, rdy = r1 * c.lens_radius;
+        float offx = u * rdx, offy = v * rdy, offz = 0.f;
+        float omv = 1.f - v;
+        S.ox = c.ox + offx; S.oy = c.oy + offy; S.oz = c.oz + offz;
+        S.dx = ((c.llx + c.hx * u) + c.vx * omv) - offx;
+        S.dy = ((c.lly + c.hy * u) + c.vy * omv) - offy;
+        S.dz = ((c.llz + c.hz * u) + c.vz * omv) - offz;
+    } else if (kind >= 0) {
+        bool scattered = true;
+        f3 nd;
+        if (kind == 0) {                                                  // lambert, src/raytracer.hxx:128-140
+            nd = mk3(((p.x + n.x) + r0) - p.x, ((p.y + n.y) + r1) - p.y, ((p.z + n.z) + r2) - p.z);
+        } else if (kind == 1) {                                           // metal, src/raytracer.hxx:142-156
+            nd = mk3(refl.x + r0 * m.w, refl.y + r1 * m.w, refl.z + r2 * m.w);
+            scattered = dot3(nd, n) > 0.f;
+        } else {                                                          // dielectric, src/raytracer.hxx:180-192
+            nd = (r0 < prob) ? refl : refr;
+        }
+        if (scattered) {
+            S.ox = p.x; S.oy = p.y; S.oz = p.z;
+            S.dx = nd.x; S.dy = nd.y; S.dz = nd.z;
+            S.ar *= m.x; S.ag *= m.y; S.ab *= m.z;                        // src/main.cxx:65
+            ++S.bounce;
+        } else {
+            ++ts.absorbed;                                                // returns black, src/main.cxx:68
+            S.st = ST_DEAD;                                               // regenerated in the next pass
+        }
+    }
+}
+
+template <bool LBVH>
+__global__ void __launch_bounds__(RT_THREADS, 2) k_render(const __grid_constant__ RtRenderArgs A)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
+    float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
+    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
+
+    stage_spheres(s_sph, A.sc.sph, A.sc.npad, bar);
+
+    PathSlot S[RT_RPT];
+#pragma unroll
+    for (int r = 0; r < RT_RPT; ++r) {
+        S[r].st = ST_EMPTY; S[r].pix = 0; S[r].smp = 0; S[r].bounce = 0;
+        S[r].ox = S[r].oy = S[r].oz = 0.f; S[r].dx = S[r].dy = S[r].dz = 0.f;
+        S[r].ar = S[r].ag = S[r].ab = 1.f;
+    }
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+    ThreadStats ts = {0, 0, 0, 0, 0};
+    float best_t[RT_RPT]; int best_i[RT_RPT];
+#pragma unroll
+    for (int r = 0; r < RT_RPT; ++r) { best_t[r] = FLT_MAX; best_i[r] = -1; }
+
+    for (;;) {
+        bool any_live = false;
+#pragma unroll
+        for (int r = 0; r < RT_RPT; ++r) {
+            shade_slot(A, s_sph, S[r], best_t[r], best_i[r], pool, ts);
+            any_live |= (S[r].st != ST_EMPTY);
+        }
+        if (!__any_sync(RT_FULL, any_live)) break;
+
+        bool live[RT_RPT];
+        float ox[RT_RPT], oy[RT_RPT], oz[RT_RPT], dx[RT_RPT], dy[RT_RPT], dz[RT_RPT];
+#pragma unroll
+        for (int r = 0; r < RT_RPT; ++r) {
+            live[r] = (S[r].st == ST_ACTIVE);
+            ox[r] = S[r].ox; oy[r] = S[r].oy; oz[r] = S[r].oz;
+            dx[r] = S[r].dx; dy[r] = S[r].dy; dz[r] = S[r].dz;
+        }
+        closest_hit_brute<RT_RPT>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+    }
+
+    // per-warp reduction of the path statistics, one atomic per counter per warp
+    uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        uint32_t x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
+        if ((threadIdx.x & 31u) == 0 && x) {
+            atomicAdd(A.stats + k, (unsigned long long)x);
+            if (k == 1 && !LBVH) atomicAdd(A.stats + 6, (unsigned long long)x * A.sc.n);   // sphere tests
+        }
+    }
+}
+
+// ------------------------------------------------------------------ parity pass: primary / caller-supplied rays
+// One thread per ray; the same two-pass brute-force closest hit.  Primary rays: u = x/W, v = y/H, lens
+// offset 0 (src/main.cxx:192-195 without jitter, src/camera.hxx:56).
+template <bool LBVH>
+__global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtHitArgs A)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
+    float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
+    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
+    stage_spheres(s_sph, A.sc.sph, A.sc.npad, bar);
+
+    const unsigned long long total = A.rays ? A.nrays : (unsigned long long)A.w * A.h;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    // every thread runs the same number of iterations: the sphere loop is warp-synchronous
+    const unsigned long long iters = (total + stride - 1) / stride;
+    for (unsigned long long it = 0; it < iters; ++it) {
+        unsigned long long i = it * stride + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+        bool live[1] = {i < total};
+        float ox[1] = {0.f}, oy[1] = {0.f}, oz[1] = {0.f}, dx[1] = {0.f}, dy[1] = {0.f}, dz[1] = {0.f};
+        if (live[0]) {
+            if (A.rays) {
+                const float *r = A.rays + 6ull * i;
+                ox[0] = r[0]; oy[0] = r[1]; oz[0] = r[2]; dx[0] = r[3]; dy[0] = r[4]; dz[0] = r[5];
+            } else {
+                uint32_t ty = (uint32_t)(i / A.w), tx = (uint32_t)(i - (unsigned long long)ty * A.w);
+                float u = (float)(A.x0 + tx) / (float)A.W;
+                float v = (float)(A.y0 + ty) / (float)A.H;
+                float omv = 1.f - v;
+                const RtDeviceCamera &c = A.cam;
+                ox[0] = c.ox; oy[0] = c.oy; oz[0] = c.oz;
+                dx[0] = (c.llx + c.hx * u) + c.vx * omv;
+                dy[0] = (c.lly + c.hy * u) + c.vy * omv;
+                dz[0] = (c.llz + c.hz * u) + c.vz * omv;
+            }
+        }
+        float bt[1]; int bi[1];
+        closest_hit_brute<1>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
+        if (live[0]) {
+            A.idx[i] = bi[0];
+            if (bi[0] >= 0) {
+                float4 s = s_sph[bi[0]];
+                float rad = __ldg(A.sc.sph_rad + bi[0]);
+                float px = ox[0] + dx[0] * bt[0], py = oy[0] + dy[0] * bt[0], pz = oz[0] + dz[0] * bt[0];
+                A.t[i] = bt[0];
+                A.normal[3 * i + 0] = (px - s.x) / rad;
+                A.normal[3 * i + 1] = (py - s.y) / rad;
+                A.normal[3 * i + 2] = (pz - s.z) / rad;
+            } else {
+                A.t[i] = 0.f;
+                A.normal[3 * i + 0] = 0.f; A.normal[3 * i + 1] = 0.f; A.normal[3 * i + 2] = 0.f;
+            }
+        }
+    }
+}
+
+}  // namespace RT_NS

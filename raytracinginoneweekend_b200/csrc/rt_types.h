@@ -1,0 +1,79 @@
+// rt_types.h -- device-side data layout shared by the kernel translation units and the C ABI.
+//
+// HBM layout (all library-owned, see DESIGN.md "Data layout"):
+//   sph      float4[npad]   {cx, cy, cz, r*r}     npad = n rounded up to 32; padding has r*r = -inf
+//   sph_rad  float [npad]   signed radius (negative = flipped normal, src/raytracer.hxx:70)
+//   sph_meta uint32[npad]   material index | kind << 30
+//   mat      float4[m]      {albedo.rgb, param}
+//   accum    ulonglong4[W*H] {R, G, B sums in 32.32 fixed point, sample count}
+//   rgb8     uchar[W*H*3], meanf float[W*H*3]  resolve outputs
+//   LBVH: nodes (2 x float4 child boxes + children), sorted primitive ids
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define RT_THREADS 256          // threads per CTA of the persistent render kernel
+#define RT_RPT 2                // camera paths resident per thread (ILP + LDS amortisation)
+#define RT_CHUNK_WORDS 16       // candidate-mask words per chunk (16 x 32 = 512 spheres)
+#define RT_BATCH 256u           // work items a warp takes from the global counter at once
+#define RT_KMIN .008f           // src/raytracer.hxx:98
+#define RT_FIXED_ONE 4294967296.f
+
+struct RtDeviceScene {
+    const float4 *sph;
+    const float *sph_rad;
+    const uint32_t *sph_meta;
+    const float4 *mat;
+    uint32_t n, npad;
+    // LBVH (rt_lbvh.cu); nodes == nullptr when not built
+    const float4 *bvh_nodes;     // 4 x float4 per inner node
+    const uint32_t *bvh_prims;   // leaf order -> sphere index
+    uint32_t bvh_root;
+};
+
+struct RtDeviceCamera {          // src/camera.hxx:66-76 derived state
+    float ox, oy, oz;
+    float llx, lly, llz;
+    float hx, hy, hz;
+    float vx, vy, vz;
+    float lens_radius;
+};
+
+struct RtRenderArgs {
+    RtDeviceScene sc;
+    RtDeviceCamera cam;
+    unsigned long long *accum;   // W*H*4
+    uint32_t W, H;               // full image
+    uint32_t x0, y0, w, h;       // tile
+    uint32_t p0, P;              // band of tile pixels [p0, p0+P) handled by this launch
+    uint32_t spp, depth, sample_base;
+    uint32_t key0, key1;
+    uint32_t total_items;        // P * spp  (< 2^31)
+    uint32_t *work_counter;      // zeroed before launch
+    unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] leaf_tests
+};
+
+struct RtHitArgs {
+    RtDeviceScene sc;
+    RtDeviceCamera cam;
+    uint32_t W, H, x0, y0, w, h; // primary pass
+    const float *rays;           // closest_hits pass: n x 6 (nullptr for the primary pass)
+    unsigned long long nrays;
+    int32_t *idx; float *t; float *normal;
+    unsigned long long *stats;
+};
+
+// launchers, one set per arithmetic mode (exact = --fmad=false TU, fast = FMA TU)
+namespace rtx {
+cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh);
+cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
+cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
+}
+namespace rtf {
+cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh);
+cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
+cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
+}
+
+size_t rt_render_smem_bytes(uint32_t npad, bool lbvh);
+size_t rt_hits_smem_bytes(uint32_t npad, bool lbvh);
