@@ -102,6 +102,8 @@ RT_EXPORT int rt_destroy(rt_ctx *ctx);
 /* Use an existing CUDA stream (e.g. torch's current stream); NULL restores the ctx's own stream. */
 RT_EXPORT int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
 RT_EXPORT int rt_sync(rt_ctx *ctx);
+/* Block until at most `max_in_flight` rt_render / rt_render_tiles calls are still running. */
+RT_EXPORT int rt_throttle(rt_ctx *ctx, uint32_t max_in_flight);
 
 /* Scene: converted on the host to the device layout (float4{c,r*r} + radius + material index;
  * float4{albedo,param} + kind) and uploaded; builds the LBVH when n > RT_BRUTE_MAX_SPHERES or
@@ -124,6 +126,12 @@ RT_EXPORT int rt_clear(rt_ctx *ctx);
 /* Trace params->spp camera paths for every pixel of `tile` and ADD them to the accumulators.
  * Asynchronous on the ctx stream; rt_sync / any readback waits. */
 RT_EXPORT int rt_render(rt_ctx *ctx, const rt_tile *tile, const rt_render_params *params);
+
+/* Same, for a LIST of tiles in ONE persistent launch (multi-GPU: the batch of tiles a rank owns or
+ * stole).  Every tile must fit in tile_w x tile_h (edge tiles may be smaller); tiles must not overlap.
+ * tile_w * tile_h * spp must stay below 2^31. */
+RT_EXPORT int rt_render_tiles(rt_ctx *ctx, const rt_tile *tiles, uint32_t ntiles, uint32_t tile_w,
+                              uint32_t tile_h, const rt_render_params *params);
 
 /* Parity pass (BASELINE config 2): primary rays, u = x/W, v = y/H, no jitter, no lens offset.
  * Host outputs, tile-shaped (h rows of w): sphere index (-1 = miss), t, normal xyz (0 on miss). */
@@ -168,12 +176,15 @@ RT_EXPORT int rt_write_ppm(const char *path, uint32_t width, uint32_t height, co
 RT_EXPORT int rt_fp32_peak_probe(rt_ctx *ctx, double out3[3]);
 
 /* ---- node-level tile queue (multi-GPU dynamic tile stealing, one process per GPU) -------------
- * A lock-free counter in POSIX shared memory, shared by the ranks of one node.  Rank 0 creates,
- * the others open.  rt_queue_next returns the previous value after adding `n` (fetch_add). */
+ * RT_QUEUE_SLOTS lock-free counters (one cache line each) in POSIX shared memory, shared by the ranks of
+ * one node: slot r is the cursor of rank r's own tile range; a rank that runs dry steals by advancing
+ * another rank's cursor.  Rank 0 creates, the others open.  rt_queue_next returns the previous value
+ * after adding `n` (fetch_add; n = 0 reads). */
 typedef struct rt_queue rt_queue;
+#define RT_QUEUE_SLOTS 64u
 RT_EXPORT int rt_queue_open(rt_queue **out, const char *name, int create);
-RT_EXPORT int rt_queue_reset(rt_queue *q, uint64_t value);
-RT_EXPORT int rt_queue_next(rt_queue *q, uint64_t n, uint64_t *previous);
+RT_EXPORT int rt_queue_reset(rt_queue *q, uint32_t slot, uint64_t value);
+RT_EXPORT int rt_queue_next(rt_queue *q, uint32_t slot, uint64_t n, uint64_t *previous);
 RT_EXPORT int rt_queue_close(rt_queue *q, int unlink_name);
 
 #ifdef __cplusplus

@@ -19,8 +19,9 @@ FLAG_BRUTE = 1 << 1
 FLAG_LBVH = 1 << 2
 
 EXPORTS = [
-    "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync",
+    "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync", "rt_throttle",
     "rt_scene_upload", "rt_camera_set", "rt_camera_get", "rt_framebuffer", "rt_clear", "rt_render",
+    "rt_render_tiles",
     "rt_primary_hits", "rt_closest_hits", "rt_readback_rgb8", "rt_readback_f32", "rt_readback_accum",
     "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
     "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe",
@@ -83,12 +84,14 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_destroy.argtypes = [vp]
     lib.rt_set_stream.argtypes = [vp, vp]
     lib.rt_sync.argtypes = [vp]
+    lib.rt_throttle.argtypes = [vp, u32]
     lib.rt_scene_upload.argtypes = [vp, vp, u32, vp, u32]
     lib.rt_camera_set.argtypes = [vp, fp, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float]
     lib.rt_camera_get.argtypes = [vp, fp]
     lib.rt_framebuffer.argtypes = [vp, u32, u32]
     lib.rt_clear.argtypes = [vp]
     lib.rt_render.argtypes = [vp, C.POINTER(RtTile), C.POINTER(RtRenderParams)]
+    lib.rt_render_tiles.argtypes = [vp, vp, u32, u32, u32, C.POINTER(RtRenderParams)]
     lib.rt_primary_hits.argtypes = [vp, C.POINTER(RtTile), u32, vp, vp, vp]
     lib.rt_closest_hits.argtypes = [vp, vp, u64, u32, vp, vp, vp]
     lib.rt_readback_rgb8.argtypes = [vp, vp]
@@ -103,8 +106,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_write_ppm.argtypes = [C.c_char_p, u32, u32, vp]
     lib.rt_fp32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     lib.rt_queue_open.argtypes = [C.POINTER(vp), C.c_char_p, i32]
-    lib.rt_queue_reset.argtypes = [vp, u64]
-    lib.rt_queue_next.argtypes = [vp, u64, C.POINTER(u64)]
+    lib.rt_queue_reset.argtypes = [vp, u32, u64]
+    lib.rt_queue_next.argtypes = [vp, u32, u64, C.POINTER(u64)]
     lib.rt_queue_close.argtypes = [vp, i32]
     for name in EXPORTS:
         fn = getattr(lib, name)
@@ -183,12 +186,21 @@ class Backend:
     def sync(self):
         _check(self.lib, self.lib.rt_sync(self.ctx))
 
+    def throttle(self, max_in_flight):
+        _check(self.lib, self.lib.rt_throttle(self.ctx, int(max_in_flight)))
+
     # ---- rendering ----------------------------------------------------------
     def render(self, spp, max_depth=50, seed=1, tile=None, sample_base=0, flags=0):
         x0, y0, w, h = tile if tile is not None else (0, 0, self.W, self.H)
         t = RtTile(x0, y0, w, h)
         p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
         _check(self.lib, self.lib.rt_render(self.ctx, C.byref(t), C.byref(p)))
+
+    def render_tiles(self, tiles, tile_w, tile_h, spp, max_depth=50, seed=1, sample_base=0, flags=0):
+        """tiles: (n,4) uint32 array of {x0,y0,w,h}; one persistent launch for the whole list."""
+        tiles = np.ascontiguousarray(tiles, np.uint32).reshape(-1, 4)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
+        _check(self.lib, self.lib.rt_render_tiles(self.ctx, tiles.ctypes.data, tiles.shape[0], int(tile_w), int(tile_h), C.byref(p)))
 
     def primary_hits(self, tile=None, flags=FLAG_EXACT):
         x0, y0, w, h = tile if tile is not None else (0, 0, self.W, self.H)
@@ -280,12 +292,13 @@ class TileQueue:
         self.create = create
         _check(self.lib, self.lib.rt_queue_open(C.byref(self.q), name.encode(), 1 if create else 0))
 
-    def reset(self, value=0):
-        _check(self.lib, self.lib.rt_queue_reset(self.q, int(value)))
+    def reset(self, slot=0, value=0):
+        _check(self.lib, self.lib.rt_queue_reset(self.q, int(slot), int(value)))
 
-    def next(self, n=1) -> int:
+    def next(self, slot=0, n=1) -> int:
+        """fetch_add(n) on counter `slot`; returns the previous value (n = 0 just reads)."""
         prev = C.c_uint64()
-        _check(self.lib, self.lib.rt_queue_next(self.q, int(n), C.byref(prev)))
+        _check(self.lib, self.lib.rt_queue_next(self.q, int(slot), int(n), C.byref(prev)))
         return int(prev.value)
 
     def close(self):

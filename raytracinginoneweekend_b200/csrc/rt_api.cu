@@ -247,6 +247,24 @@ int rt_sync(rt_ctx *c)
     return drain_events(c);
 }
 
+int rt_throttle(rt_ctx *c, uint32_t max_in_flight)
+{
+    if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    // render calls complete in submission order (one stream): retire the oldest until few enough remain
+    while (c->pending.size() > max_in_flight) {
+        EventPair p = c->pending.front();
+        CK(cudaEventSynchronize(p.b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, p.a, p.b));
+        c->hs.render_ms += ms;
+        c->hs.last_render_ms = ms;
+        c->free_events.push_back(p);
+        c->pending.erase(c->pending.begin());
+    }
+    return RT_OK;
+}
+
 int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_material *materials, uint32_t m)
 {
     if (!c || !spheres || !materials || n == 0 || m == 0) return fail(RT_ERR_INVALID, "rt_scene_upload: empty scene or NULL argument");
@@ -366,17 +384,24 @@ int rt_clear(rt_ctx *c)
     return RT_OK;
 }
 
-int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
+// Common scheduling of one or more launches over a tile list.  `tiles` all fit in tw x th pixel slots.
+static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, uint32_t tw, uint32_t th,
+                             const rt_render_params *p)
 {
-    if (!c || !tile || !p) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
     if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_render: no scene uploaded");
     if (!c->have_cam) return fail(RT_ERR_INVALID, "rt_render: no camera set");
     if (!c->d_accum) return fail(RT_ERR_INVALID, "rt_render: no framebuffer");
     if (p->max_depth == 0) return fail(RT_ERR_INVALID, "rt_render: max_depth must be >= 1");
-    if (tile->w == 0 || tile->h == 0 || p->spp == 0) return RT_OK;   // empty tile / zero samples: nothing to add
-    if ((unsigned long long)tile->x0 + tile->w > c->W || (unsigned long long)tile->y0 + tile->h > c->H)
-        return fail(RT_ERR_INVALID, "rt_render: tile outside the framebuffer");
     if ((unsigned long long)p->sample_base + p->spp > 0xffffffffull) return fail(RT_ERR_INVALID, "rt_render: sample index overflow");
+    if (ntiles == 0 || p->spp == 0 || tw == 0 || th == 0) return RT_OK;   // nothing to add
+    for (uint32_t i = 0; i < ntiles; ++i) {
+        const rt_tile &t = tiles[i];
+        if ((unsigned long long)t.x0 + t.w > c->W || (unsigned long long)t.y0 + t.h > c->H)
+            return fail(RT_ERR_INVALID, "rt_render: tile outside the framebuffer");
+        if (t.w > tw || t.h > th) return fail(RT_ERR_INVALID, "rt_render_tiles: tile larger than the nominal tile size");
+    }
+    const unsigned long long TP = (unsigned long long)tw * th;
+    if (TP * p->spp >= (1ull << 31)) return fail(RT_ERR_INVALID, "rt_render: tile_pixels * spp must stay below 2^31; use smaller tiles or split spp with sample_base");
     CK(cudaSetDevice(c->device));
 
     const bool exact = (p->flags & RT_FLAG_EXACT) != 0;
@@ -393,7 +418,15 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
     if (r) return r;
     CK(cudaEventRecord(ev.a, c->stream));
 
-    CK(rt_launch_add_count(c->d_accum, c->W, tile->x0, tile->y0, tile->w, tile->h, p->spp, c->stream));
+    uint4 *d_tiles = nullptr;
+    uint4 tile0 = make_uint4(tiles[0].x0, tiles[0].y0, tiles[0].w, tiles[0].h);
+    if (ntiles > 1) {
+        static_assert(sizeof(rt_tile) == sizeof(uint4), "rt_tile must be 16 bytes");
+        CK(cudaMallocAsync((void **)&d_tiles, (size_t)ntiles * sizeof(uint4), c->stream));
+        // pageable source: the runtime stages the bytes before returning, so `tiles` may be reused by the caller
+        CK(cudaMemcpyAsync(d_tiles, tiles, (size_t)ntiles * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+    }
+    CK(rt_launch_add_count(c->d_accum, c->W, tile0, d_tiles, ntiles, (uint32_t)TP, p->spp, c->stream));
     c->hs.launches += 1;
 
     RtRenderArgs a{};
@@ -401,19 +434,19 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
     a.cam = c->cam;
     a.accum = c->d_accum;
     a.W = c->W; a.H = c->H;
-    a.x0 = tile->x0; a.y0 = tile->y0; a.w = tile->w; a.h = tile->h;
+    a.tile0 = tile0;
+    a.tiles = d_tiles;
+    a.TP = (uint32_t)TP;
     a.spp = p->spp; a.depth = p->max_depth; a.sample_base = p->sample_base;
     a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
     a.stats = c->d_stats;
 
-    // bands of tile pixels so that items = P * spp stays below 2^31 (32-bit item arithmetic in the kernel)
-    const unsigned long long npx = (unsigned long long)tile->w * tile->h;
-    unsigned long long P = npx;
-    if (npx * p->spp >= (1ull << 31)) P = ((1ull << 31) - 1) / p->spp;
-    if (P == 0) return fail(RT_ERR_INVALID, "rt_render: spp too large");
-    for (unsigned long long p0 = 0; p0 < npx; p0 += P) {
-        a.p0 = (uint32_t)p0;
-        a.P = (uint32_t)((npx - p0 < P) ? (npx - p0) : P);
+    // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic)
+    uint32_t per_band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);
+    for (uint32_t t0 = 0; t0 < ntiles; t0 += per_band) {
+        uint32_t nt = (ntiles - t0 < per_band) ? (ntiles - t0) : per_band;
+        a.t0 = t0;
+        a.P = nt * (uint32_t)TP;
         a.total_items = a.P * p->spp;
         if (c->counter_slot == kCounterRing) {
             CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
@@ -429,9 +462,40 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
     }
+    if (d_tiles) CK(cudaFreeAsync(d_tiles, c->stream));
     CK(cudaEventRecord(ev.b, c->stream));
     c->pending.push_back(ev);
     return RT_OK;
+}
+
+int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
+{
+    if (!c || !tile || !p) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
+    if (tile->w == 0 || tile->h == 0 || p->spp == 0) {
+        // still validate the call order so errors do not depend on the tile being empty
+        if (!c->d_sph || !c->have_cam || !c->d_accum) return render_tiles_impl(c, tile, 1, 1, 1, p);
+        return RT_OK;
+    }
+    const unsigned long long npx = (unsigned long long)tile->w * tile->h;
+    if (npx * p->spp < (1ull << 31)) return render_tiles_impl(c, tile, 1, tile->w, tile->h, p);
+    // big rectangle: cut it into row strips whose item count fits 31 bits and run them as one tile list
+    unsigned long long rows = (((1ull << 31) - 1) / p->spp) / tile->w;
+    if (rows == 0) return fail(RT_ERR_INVALID, "rt_render: width * spp must stay below 2^31; split spp with sample_base");
+    if (rows > tile->h) rows = tile->h;
+    std::vector<rt_tile> strips;
+    for (uint32_t y = 0; y < tile->h; y += (uint32_t)rows) {
+        uint32_t h = (tile->h - y < rows) ? (tile->h - y) : (uint32_t)rows;
+        strips.push_back(rt_tile{tile->x0, tile->y0 + y, tile->w, h});
+    }
+    return render_tiles_impl(c, strips.data(), (uint32_t)strips.size(), tile->w, (uint32_t)rows, p);
+}
+
+int rt_render_tiles(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, uint32_t tile_w, uint32_t tile_h,
+                    const rt_render_params *p)
+{
+    if (!c || !p || (ntiles && !tiles)) return fail(RT_ERR_INVALID, "rt_render_tiles: NULL argument");
+    if (ntiles == 0) return RT_OK;
+    return render_tiles_impl(c, tiles, ntiles, tile_w, tile_h, p);
 }
 
 static int hits_common(rt_ctx *c, RtHitArgs &a, unsigned long long total, uint32_t flags,
@@ -642,10 +706,11 @@ int rt_fp32_peak_probe(rt_ctx *c, double out[3])
 
 // ---------------------------------------------------------------- node-level tile queue (POSIX shm)
 struct rt_queue {
-    std::atomic<uint64_t> *ctr;
+    std::atomic<uint64_t> *ctr;   // RT_QUEUE_SLOTS counters, 64-byte stride
     std::string name;
     int fd;
 };
+static const size_t kQueueBytes = 64 * RT_QUEUE_SLOTS;
 
 int rt_queue_open(rt_queue **out, const char *name, int create)
 {
@@ -653,37 +718,37 @@ int rt_queue_open(rt_queue **out, const char *name, int create)
     static_assert(sizeof(std::atomic<uint64_t>) == 8, "lock-free 64-bit atomic expected");
     int fd = shm_open(name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
     if (fd < 0) return fail(RT_ERR_SYS, std::string("shm_open(") + name + "): " + std::strerror(errno));
-    if (create && ftruncate(fd, 4096) != 0) { int e = errno; close(fd); return fail(RT_ERR_SYS, std::string("ftruncate: ") + std::strerror(e)); }
-    void *p = mmap(nullptr, 4096, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (create && ftruncate(fd, (off_t)kQueueBytes) != 0) { int e = errno; close(fd); return fail(RT_ERR_SYS, std::string("ftruncate: ") + std::strerror(e)); }
+    void *p = mmap(nullptr, kQueueBytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
     if (p == MAP_FAILED) { int e = errno; close(fd); return fail(RT_ERR_SYS, std::string("mmap: ") + std::strerror(e)); }
     rt_queue *q = new (std::nothrow) rt_queue();
-    if (!q) { munmap(p, 4096); close(fd); return fail(RT_ERR_SYS, "out of host memory"); }
+    if (!q) { munmap(p, kQueueBytes); close(fd); return fail(RT_ERR_SYS, "out of host memory"); }
     q->ctr = reinterpret_cast<std::atomic<uint64_t> *>(p);
     q->name = name;
     q->fd = fd;
-    if (create) q->ctr->store(0, std::memory_order_seq_cst);
+    if (create) for (uint32_t s = 0; s < RT_QUEUE_SLOTS; ++s) q->ctr[8 * s].store(0, std::memory_order_seq_cst);
     *out = q;
     return RT_OK;
 }
 
-int rt_queue_reset(rt_queue *q, uint64_t value)
+int rt_queue_reset(rt_queue *q, uint32_t slot, uint64_t value)
 {
-    if (!q) return fail(RT_ERR_INVALID, "queue is NULL");
-    q->ctr->store(value, std::memory_order_seq_cst);
+    if (!q || slot >= RT_QUEUE_SLOTS) return fail(RT_ERR_INVALID, "rt_queue_reset: bad queue or slot");
+    q->ctr[8 * slot].store(value, std::memory_order_seq_cst);
     return RT_OK;
 }
 
-int rt_queue_next(rt_queue *q, uint64_t n, uint64_t *previous)
+int rt_queue_next(rt_queue *q, uint32_t slot, uint64_t n, uint64_t *previous)
 {
-    if (!q || !previous) return fail(RT_ERR_INVALID, "rt_queue_next: NULL argument");
-    *previous = q->ctr->fetch_add(n, std::memory_order_seq_cst);
+    if (!q || !previous || slot >= RT_QUEUE_SLOTS) return fail(RT_ERR_INVALID, "rt_queue_next: bad queue, slot or NULL argument");
+    *previous = q->ctr[8 * slot].fetch_add(n, std::memory_order_seq_cst);
     return RT_OK;
 }
 
 int rt_queue_close(rt_queue *q, int unlink_name)
 {
     if (!q) return RT_OK;
-    munmap((void *)q->ctr, 4096);
+    munmap((void *)q->ctr, kQueueBytes);
     close(q->fd);
     if (unlink_name) shm_unlink(q->name.c_str());
     delete q;

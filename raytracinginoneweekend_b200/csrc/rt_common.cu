@@ -13,14 +13,17 @@ size_t rt_hits_smem_bytes(uint32_t npad, bool lbvh)
     return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * 1 * RT_THREADS * 4u;
 }
 
-// count += spp for every pixel of the tile (the 4th accumulator channel).
-__global__ void k_add_count(unsigned long long *accum, uint32_t W, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
-                            unsigned long long spp)
+// count += spp for every pixel of the listed tiles (the 4th accumulator channel).
+__global__ void k_add_count(unsigned long long *accum, uint32_t W, uint4 tile0, const uint4 *tiles, uint32_t nt,
+                            uint32_t TP, unsigned long long spp)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= w * h) return;
-    uint32_t ty = i / w, tx = i - ty * w;
-    accum[4ull * ((unsigned long long)(y0 + ty) * W + x0 + tx) + 3] += spp;
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (unsigned long long)nt * TP) return;
+    uint32_t tl = (uint32_t)(i / TP), r = (uint32_t)(i - (unsigned long long)tl * TP);
+    uint4 T = tiles ? tiles[tl] : tile0;
+    if (r >= T.z * T.w) return;
+    uint32_t ty = r / T.z, tx = r - ty * T.z;
+    accum[4ull * ((unsigned long long)(T.y + ty) * W + T.x + tx) + 3] += spp;
 }
 
 // mean = sum / (count * 2^32) in double, rounded to float (src/main.cxx:205-207: sum / spp);
@@ -91,12 +94,12 @@ __global__ void __launch_bounds__(256) k_fp32_probe(float *out, float a, float b
     if (s == 123.456f) out[0] = s;   // keeps the chains alive without a store on the timed path
 }
 
-cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
-                                unsigned long long spp, cudaStream_t s)
+cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint4 tile0, const uint4 *tiles, uint32_t nt,
+                                uint32_t TP, unsigned long long spp, cudaStream_t s)
 {
-    uint32_t n = w * h;
+    unsigned long long n = (unsigned long long)nt * TP;
     if (!n) return cudaSuccess;
-    k_add_count<<<(n + 255) / 256, 256, 0, s>>>(accum, W, x0, y0, w, h, spp);
+    k_add_count<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(accum, W, tile0, tiles, nt, TP, spp);
     return cudaGetLastError();
 }
 

@@ -2,8 +2,8 @@
 #pragma once
 #include "rt_types.h"
 
-cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint32_t x0, uint32_t y0, uint32_t w, uint32_t h,
-                                unsigned long long spp, cudaStream_t s);
+cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint4 tile0, const uint4 *tiles, uint32_t nt,
+                                uint32_t TP, unsigned long long spp, cudaStream_t s);
 cudaError_t rt_launch_resolve(const unsigned long long *accum, unsigned long long npix, unsigned char *rgb8, float *meanf,
                               cudaStream_t s);
 cudaError_t rt_launch_fp32_probe(float *scratch, int blocks, int iters, cudaStream_t s);

@@ -345,27 +345,37 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     }
 
     // ---- regeneration: give every ended path a new (pixel, sample)
-    uint32_t item = pool_take(pool, want, A.work_counter, A.total_items);
     uint32_t px = 0, py = 0;
     uint32_t ev = S.bounce + 1u;
-    if (want) {
-        if (item != 0xffffffffu) {
-            uint32_t s_i = item / A.P;
-            uint32_t q = A.p0 + (item - s_i * A.P);
-            uint32_t ty = q / A.w;
-            px = A.x0 + (q - ty * A.w);
-            py = A.y0 + ty;
-            S.pix = py * A.W + px;
-            S.smp = A.sample_base + s_i;
-            S.bounce = 0;
-            S.ar = S.ag = S.ab = 1.f;
-            S.st = ST_ACTIVE;
-            ev = 0;
-            mode = RM_CAMERA;
-            ++ts.samples;
-        } else {
-            S.st = ST_EMPTY;
+    for (bool need = want;;) {
+        uint32_t item = pool_take(pool, need, A.work_counter, A.total_items);
+        if (need) {
+            if (item != 0xffffffffu) {
+                uint32_t s_i = item / A.P;
+                uint32_t q = item - s_i * A.P;
+                uint32_t tl = q / A.TP;
+                uint32_t r = q - tl * A.TP;
+                uint4 T = A.tiles ? __ldg(A.tiles + A.t0 + tl) : A.tile0;
+                if (r < T.z * T.w) {                                      // edge tiles leave slots unused
+                    uint32_t ty = r / T.z;
+                    px = T.x + (r - ty * T.z);
+                    py = T.y + ty;
+                    S.pix = py * A.W + px;
+                    S.smp = A.sample_base + s_i;
+                    S.bounce = 0;
+                    S.ar = S.ag = S.ab = 1.f;
+                    S.st = ST_ACTIVE;
+                    ev = 0;
+                    mode = RM_CAMERA;
+                    ++ts.samples;
+                    need = false;
+                }
+            } else {
+                S.st = ST_EMPTY;
+                need = false;
+            }
         }
+        if (!__any_sync(RT_FULL, need)) break;
     }
 
     // ---- one Philox loop serves camera jitter, lens / lambert / metal ball samples and the dielectric coin

@@ -44,13 +44,18 @@ struct RtRenderArgs {
     RtDeviceCamera cam;
     unsigned long long *accum;   // W*H*4
     uint32_t W, H;               // full image
-    uint32_t x0, y0, w, h;       // tile
-    uint32_t p0, P;              // band of tile pixels [p0, p0+P) handled by this launch
+    // Work domain of one launch: `nt` tiles, each allotted TP = tw*th pixel slots (edge tiles are
+    // smaller and leave slots unused), times spp samples.  item -> (sample, tile, pixel-in-tile).
+    uint4 tile0;                 // {x0,y0,w,h} when tiles == nullptr (single-tile launch)
+    const uint4 *tiles;          // device tile list {x0,y0,w,h} or nullptr
+    uint32_t t0;                 // first list entry of this launch
+    uint32_t TP;                 // pixel slots per tile (nominal tile width * height)
+    uint32_t P;                  // pixel slots of this launch = nt * TP
     uint32_t spp, depth, sample_base;
     uint32_t key0, key1;
     uint32_t total_items;        // P * spp  (< 2^31)
     uint32_t *work_counter;      // zeroed before launch
-    unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] leaf_tests
+    unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] sphere tests
 };
 
 struct RtHitArgs {

@@ -1,0 +1,145 @@
+"""One process per GPU: tile sharding with dynamic stealing + framebuffer gather to rank 0.
+
+The reference has no multi-GPU path; this is new work that BASELINE.json's
+north_star asks for.  Pixels are independent, so the only exchange is the final framebuffer:
+
+* the image is cut into small tiles, tile indices are split into one contiguous range per rank;
+* every rank owns a cursor (one cache line in POSIX shared memory, ``rt_queue_*``); it takes guided
+  chunks from its own range first (half of what is left, so a rank needs only O(log n) persistent
+  launches) and, when that is dry, steals chunks from the other ranks' cursors -- the path-length
+  tail and the sky/glass cost gap make per-tile cost vary by >10x, static splits do not balance;
+* each chunk is ONE ``rt_render_tiles`` launch (a persistent kernel over the tile list); at most
+  two chunks are in flight per GPU, so stealing reacts to real progress;
+* every rank resolves its tiles to RGB8 (pixels it did not render stay 0) and the frame is gathered on
+  rank 0 with one NCCL ``reduce(SUM)`` over NVLink -- tiles are disjoint, so the sum is the union.
+
+No data-path collective other than that gather.  The scheduler is CUDA-free and is exercised on CPU
+with the gloo backend (tests/test_multigpu_cpu.py).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def make_tiles(W: int, H: int, tw: int, th: int) -> np.ndarray:
+    """Row-major grid of {x0,y0,w,h} tiles covering W x H; edge tiles are smaller."""
+    xs = np.arange(0, W, tw, dtype=np.int64)
+    ys = np.arange(0, H, th, dtype=np.int64)
+    out = np.empty((len(ys) * len(xs), 4), np.uint32)
+    k = 0
+    for y in ys:
+        for x in xs:
+            out[k] = (x, y, min(tw, W - x), min(th, H - y))
+            k += 1
+    return out
+
+
+def rank_ranges(ntiles: int, world: int):
+    """Contiguous [lo, hi) range of tile indices per rank."""
+    return [(r * ntiles // world, (r + 1) * ntiles // world) for r in range(world)]
+
+
+class StealingScheduler:
+    """Guided self-scheduling on per-rank cursors with stealing.
+
+    ``queue`` needs ``reset(slot, value)`` and ``next(slot, n) -> previous`` (fetch_add; n=0 reads):
+    ``backend.TileQueue`` in production, any in-process fake in tests.
+    """
+
+    def __init__(self, queue, rank: int, world: int, ntiles: int, min_chunk: int = 1):
+        self.q, self.rank, self.world, self.ntiles = queue, rank, world, ntiles
+        self.ranges = rank_ranges(ntiles, world)
+        self.min_chunk = max(1, int(min_chunk))
+        self.own_taken = 0
+        self.stolen = 0
+
+    def reset_own(self):
+        """Every rank rewinds its own cursor; the caller must barrier before anyone pulls."""
+        self.q.reset(self.rank, self.ranges[self.rank][0])
+        self.own_taken = 0
+        self.stolen = 0
+
+    def _take(self, victim: int):
+        lo, hi = self.ranges[victim]
+        cur = self.q.next(victim, 0)
+        remaining = hi - cur
+        if remaining <= 0:
+            return None
+        if victim == self.rank:
+            k = max(self.min_chunk, (remaining + 1) // 2)
+        else:
+            k = max(self.min_chunk, remaining // (2 * self.world))
+        start = self.q.next(victim, k)
+        if start >= hi:
+            return None
+        return start, min(k, hi - start)
+
+    def next_batch(self):
+        """(start, count, victim_rank) of the next chunk of tile indices, or None when all is taken."""
+        order = [self.rank] + [(self.rank + d) % self.world for d in range(1, self.world)]
+        for victim in order:
+            got = self._take(victim)
+            if got is not None:
+                if victim == self.rank:
+                    self.own_taken += got[1]
+                else:
+                    self.stolen += got[1]
+                return got[0], got[1], victim
+        return None
+
+
+def render_distributed(renderer, sched: StealingScheduler, tiles: np.ndarray, barrier, max_in_flight: int = 2):
+    """Drive one frame on this rank.  ``renderer.render_tiles(tile_array)`` submits one asynchronous
+    launch; ``renderer.throttle(n)`` blocks until at most n launches are in flight.
+    Returns the number of tiles this rank rendered."""
+    sched.reset_own()
+    barrier()                       # all cursors are rewound before anyone pulls
+    done = 0
+    while True:
+        b = sched.next_batch()
+        if b is None:
+            break
+        start, count, _ = b
+        renderer.render_tiles(tiles[start:start + count])
+        done += count
+        renderer.throttle(max_in_flight - 1)
+    renderer.throttle(0)
+    barrier()                       # nobody rewinds a cursor while another rank may still be stealing from it
+    return done
+
+
+class CudaTileRenderer:
+    """Adapter: backend.Backend -> the renderer protocol of render_distributed."""
+
+    def __init__(self, backend, tile_w, tile_h, spp, max_depth, seed, flags=0):
+        self.be, self.tw, self.th = backend, tile_w, tile_h
+        self.spp, self.depth, self.seed, self.flags = spp, max_depth, seed, flags
+
+    def render_tiles(self, tiles):
+        self.be.render_tiles(tiles, self.tw, self.th, self.spp, self.depth, self.seed, 0, self.flags)
+
+    def throttle(self, n):
+        self.be.throttle(n)
+
+
+def device_rgb8_tensor(backend):
+    """Zero-copy torch view (uint8, H*W*3) of the backend's device RGB8 buffer."""
+    import torch
+
+    ptr, nbytes = backend.device_rgb8()
+
+    class _Holder:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+    return torch.as_tensor(_Holder(), device=f"cuda:{backend.device}")
+
+
+def gather_frame(backend, dist=None, dst: int = 0):
+    """Resolve locally, then reduce(SUM) the RGB8 frame to rank `dst` (NCCL over NVLink when world > 1).
+    Returns the torch tensor view (valid on `dst`)."""
+    backend.resolve_device()
+    backend.sync()                   # the resolve ran on the ctx stream; NCCL uses torch's stream
+    t = device_rgb8_tensor(backend)
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.reduce(t, dst=dst, op=dist.ReduceOp.SUM)
+    return t

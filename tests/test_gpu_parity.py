@@ -1,0 +1,265 @@
+"""GPU parity tests (run on the B200 box with `-m gpu`).  Everything goes through the C ABI
+(librtiow_b200.so via ctypes); the CPU oracle is only the checker.
+
+Bars (BASELINE.json north_star):
+  * primary rays, 1 spp, no jitter: hit sphere index bit-exact, t / normal within 1e-5 relative
+    (the exact mode is expected -- and asserted -- to be 0 ulp);
+  * full renders: per-pixel RMSE and mean luminance within the Monte Carlo noise bound against the
+    reference CPU render; in exact mode, additionally BIT-EXACT accumulators against the oracle port
+    driven by the same counter-based RNG.
+"""
+import numpy as np
+import pytest
+
+from conftest import assert_bits_equal
+from raytracinginoneweekend_b200 import scenes
+from raytracinginoneweekend_b200.backend import FLAG_BRUTE, FLAG_EXACT, FLAG_LBVH, RtError
+
+pytestmark = pytest.mark.gpu
+
+RNG_PHILOX = 1
+
+
+def setup(be, sc, W, H):
+    be.upload_scene(sc)
+    be.framebuffer(W, H)
+    be.reset_stats()
+
+
+# ------------------------------------------------------------------ config 2: primary rays
+def test_primary_hits_match_reference_fixture(be, golden):
+    """Against tests/golden/primary.npz, produced by the compiled reference's hit_world/intersect."""
+    g = golden("primary")
+    for name in ("huge", "simple"):
+        W, H = (int(x) for x in g[f"{name}_wh"])
+        setup(be, scenes.get_scene(name, W, H).with_camera(aperture=0.0), W, H)
+        idx, t, nrm = be.primary_hits(flags=FLAG_EXACT)
+        assert_bits_equal(idx.astype(np.int16), g[f"{name}_idx"], f"{name} hit index")
+        assert_bits_equal(t, g[f"{name}_t"], f"{name} t")
+        assert_bits_equal(nrm, g[f"{name}_n"], f"{name} normal")
+
+
+def test_primary_hits_config2_full_size(be, port):
+    """BASELINE config 2: huge-scene 1280x720, 1 spp, no jitter -- hit index bit-exact, t and normal
+    within 1e-5 relative (asserted at 0 ulp) against the oracle."""
+    W, H = 1280, 720
+    sc = scenes.huge_scene(W, H).with_camera(aperture=0.0)
+    setup(be, sc, W, H)
+    idx, t, nrm = be.primary_hits(flags=FLAG_EXACT)
+    oi, ot, on = port.primary_hits(sc, W, H, nthreads=64)
+    assert_bits_equal(idx, oi, "hit index")
+    rel_t = np.abs(t - ot) / np.maximum(np.abs(ot), 1e-30)
+    rel_n = np.abs(nrm - on) / np.maximum(np.abs(on), 1e-30)
+    assert rel_t.max() <= 1e-5 and rel_n.max() <= 1e-5     # the stated tolerance
+    assert_bits_equal(t, ot, "t")                            # ... and in fact 0 ulp
+    assert_bits_equal(nrm, on, "normal")
+    assert len(np.unique(idx)) > 300 and (idx < 0).any()
+    # the throughput (FMA) build must agree on (nearly) every pixel; differences can only sit on silhouettes
+    fi, ft, fn = be.primary_hits(flags=0)
+    assert (fi != oi).mean() < 2e-4
+    # tiles of the same pass
+    ti, tt, tn = be.primary_hits(tile=(37, 11, 501, 97), flags=FLAG_EXACT)
+    assert_bits_equal(ti, oi[11:108, 37:538], "tile hit index")
+    assert_bits_equal(tt, ot[11:108, 37:538], "tile t")
+
+
+@pytest.mark.parametrize("n_side", [1, 5, 30, 46])
+def test_closest_hits_arbitrary_rays(be, port, n_side):
+    """Bounce-like rays (origins on/inside/outside spheres) over scenes of 2..2117 spheres: covers
+    n not a multiple of 32, one chunk (<=512) and several chunks, ties, the second root and kMIN."""
+    sc = scenes.synthetic_scene(n_side=n_side, width=64, height=36)
+    rng = np.random.default_rng(n_side)
+    n = 20000
+    o = np.empty((n, 3), np.float32)
+    pick = rng.integers(0, sc.n, n)
+    c, r = sc.spheres[pick, :3], sc.spheres[pick, 3:4]
+    dirs = rng.normal(size=(n, 3)).astype(np.float32)
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True).astype(np.float32)
+    o[:] = c + dirs * np.abs(r) * rng.choice(np.float32([0.0, 0.5, 1.0, 1.0, 1.5, 8.0]), (n, 1))
+    d = rng.normal(size=(n, 3)).astype(np.float32) * rng.choice(np.float32([1e-3, 1.0, 1.0, 50.0]), (n, 1))
+    rays = np.concatenate([o, d], 1).astype(np.float32)
+    be.upload_scene(sc)
+    gi, gt, gn = be.closest_hits(rays, flags=FLAG_EXACT | FLAG_BRUTE)
+    oi, ot, on, _ = port.closest_hits(sc, rays)
+    assert_bits_equal(gi, oi, "index")
+    assert_bits_equal(gt, ot, "t")
+    assert_bits_equal(gn, on, "normal")
+    assert (oi >= 0).mean() > .2
+
+
+# ------------------------------------------------------------------ full renders, exact mode: bit-exact
+@pytest.mark.parametrize("name,W,H,spp,depth", [("simple", 96, 54, 4, 50), ("huge", 96, 54, 3, 50),
+                                                 ("huge", 33, 7, 2, 5), ("simple", 31, 17, 5, 1)])
+def test_exact_render_is_bit_identical_to_oracle(be, port, name, W, H, spp, depth):
+    sc = scenes.get_scene(name, W, H)
+    setup(be, sc, W, H)
+    be.render(spp, depth, seed=0xC0FFEE12345, flags=FLAG_EXACT)
+    acc = be.readback_accum()
+    o = port.render(sc, W, H, spp, depth, 0xC0FFEE12345, nthreads=64, rng=RNG_PHILOX, want_fixed=True)
+    assert_bits_equal(acc[..., :3], o["fixed"], "32.32 radiance sums")
+    assert (acc[..., 3] == spp).all()
+    st = be.stats()
+    assert st["samples"] == W * H * spp
+    assert st["segments"] == int(o["stats"][0])
+    assert st["sky"] == int(o["stats"][1])
+    assert st["absorbed"] + st["capped"] == int(o["stats"][2] + o["stats"][3])
+    assert st["sphere_tests"] == st["segments"] * sc.n
+    mean, u8 = port.resolve_fixed(o["fixed"], spp)
+    assert_bits_equal(be.readback_f32(), mean, "mean radiance")
+    assert_bits_equal(be.readback_rgb8(), u8, "8-bit image")
+
+
+def test_exact_render_tiles_and_sample_ranges_compose(be, port):
+    """Integer accumulation + (pixel, sample)-keyed RNG: any split into tiles, tile lists or sample
+    ranges gives exactly the accumulators of one full call."""
+    W, H, spp = 70, 41, 4
+    sc = scenes.huge_scene(W, H)
+    setup(be, sc, W, H)
+    be.render(spp, 50, seed=5, flags=FLAG_EXACT)
+    full = be.readback_accum()
+    be.clear()
+    be.render(spp, 50, seed=5, tile=(0, 0, 30, 41), flags=FLAG_EXACT)
+    be.render(spp, 50, seed=5, tile=(30, 0, 40, 20), flags=FLAG_EXACT)
+    from raytracinginoneweekend_b200.multigpu import make_tiles
+    rest = make_tiles(40, 21, 16, 8)
+    rest[:, 0] += 30
+    rest[:, 1] += 20
+    be.render_tiles(rest, 16, 8, spp, 50, seed=5, flags=FLAG_EXACT)
+    assert_bits_equal(be.readback_accum(), full, "tiles")
+    be.clear()
+    be.render(1, 50, seed=5, flags=FLAG_EXACT)
+    be.render(3, 50, seed=5, sample_base=1, flags=FLAG_EXACT)
+    assert_bits_equal(be.readback_accum(), full, "sample ranges")
+    # and the oracle agrees with the whole
+    o = port.render(sc, W, H, spp, 50, 5, nthreads=64, rng=RNG_PHILOX, want_fixed=True)
+    assert_bits_equal(full[..., :3], o["fixed"], "oracle")
+
+
+def test_fast_render_full_size_composition(be):
+    """BASELINE size (1280x720): the throughput build is deterministic and split-invariant too."""
+    W, H = 1280, 720
+    sc = scenes.huge_scene(W, H)
+    setup(be, sc, W, H)
+    be.render(2, 50, seed=1)
+    a = be.readback_accum()
+    be.clear()
+    be.render(2, 50, seed=1)
+    assert_bits_equal(be.readback_accum(), a, "run-to-run determinism")
+    be.clear()
+    from raytracinginoneweekend_b200.multigpu import make_tiles
+    tiles = make_tiles(W, H, 128, 64)
+    k = len(tiles) // 3
+    be.render_tiles(tiles[:k], 128, 64, 2, 50, seed=1)
+    be.render_tiles(tiles[k:], 128, 64, 1, 50, seed=1)
+    be.render_tiles(tiles[k:], 128, 64, 1, 50, seed=1, sample_base=1)
+    assert_bits_equal(be.readback_accum(), a, "tile lists + sample ranges")
+    assert (a[..., 3] == 2).all()
+    # checksum-of-checksums style sanity: radiance is within [0, 1] per sample
+    assert a[..., :3].max() <= 2 * (1 << 32)
+
+
+# ------------------------------------------------------------------ full renders vs the reference CPU render
+def mc_check(mean_gpu, n_gpu, g, name):
+    """RMSE <= 1.15 sqrt(mean_px(var) (1/Nref + 1/Ngpu)); |d luminance| <= 4 sigma;
+    16x16 block means within 5 sigma of their own noise."""
+    ref_mean, var = g[f"{name}_mean"].astype(np.float64), g[f"{name}_var"].astype(np.float64)
+    n_ref = int(g[f"{name}_cfg"][2])
+    k = 1.0 / n_ref + 1.0 / n_gpu
+    diff = mean_gpu.astype(np.float64) - ref_mean
+    rmse = np.sqrt((diff ** 2).mean())
+    bound = 1.15 * np.sqrt(var.mean() * k)
+    assert rmse <= bound, f"{name}: RMSE {rmse:.5f} exceeds the noise bound {bound:.5f}"
+    assert rmse >= 0.5 * np.sqrt(var.mean() * k), f"{name}: RMSE {rmse:.5f} implausibly small for independent renders"
+    wy = np.array([.2126, .7152, .0722])
+    dlum = abs((diff @ wy).mean())
+    sig = np.sqrt(((var * wy ** 2).sum(-1) * k).sum()) / diff.shape[0] / diff.shape[1]
+    assert dlum <= 4 * sig, f"{name}: mean luminance differs by {dlum:.6f} > 4 sigma = {4 * sig:.6f}"
+    H, W = diff.shape[:2]
+    hb, wb = H // 16 * 16, W // 16 * 16
+    bd = diff[:hb, :wb].reshape(hb // 16, 16, wb // 16, 16, 3).mean((1, 3))
+    bs = np.sqrt(var[:hb, :wb].reshape(hb // 16, 16, wb // 16, 16, 3).mean((1, 3)) * k / 256)
+    z = np.abs(bd) / np.maximum(bs, 1e-6)
+    assert np.percentile(z, 99) < 5.0, f"{name}: low-frequency bias, block z-score p99 = {np.percentile(z, 99):.2f}"
+    return rmse, bound, dlum, sig
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_EXACT], ids=["fast", "exact"])
+@pytest.mark.parametrize("name", ["simple", "huge"])
+def test_render_matches_reference_cpu_render_statistically(be, golden, name, flags):
+    g = golden("reference_render")
+    W, H, _, depth, _ = (int(x) for x in g[f"{name}_cfg"])
+    setup(be, scenes.get_scene(name, W, H), W, H)
+    n_gpu = 2048
+    be.render(n_gpu, depth, seed=31337, flags=flags)
+    mean = be.readback_f32()
+    rmse, bound, dlum, sig = mc_check(mean, n_gpu, g, name)
+    st = be.stats()
+    ref_seg = float(g[f"{name}_stats"][0]) / (W * H * int(g[f"{name}_cfg"][2]))
+    assert abs(st["segments"] / st["samples"] - ref_seg) < 0.02 * ref_seg     # path-length statistics agree
+    ref_cap = float(g[f"{name}_stats"][3] + g[f"{name}_stats"][2]) / (W * H * int(g[f"{name}_cfg"][2]))
+    assert abs((st["capped"] + st["absorbed"]) / st["samples"] - ref_cap) < 0.05 * ref_cap + 1e-4
+
+
+def test_fast_and_exact_builds_agree_statistically(be):
+    W, H = 160, 90
+    setup(be, scenes.huge_scene(W, H), W, H)
+    be.render(512, 50, seed=3, flags=FLAG_EXACT)
+    a = be.readback_f32().astype(np.float64)
+    be.clear()
+    be.render(512, 50, seed=3, flags=0)
+    b = be.readback_f32().astype(np.float64)
+    # same seeds and counters: almost every path is identical, a few diverge at grazing hits
+    assert np.sqrt(((a - b) ** 2).mean()) < 0.01
+    assert abs(a.mean() - b.mean()) < 1e-3
+
+
+# ------------------------------------------------------------------ resolve + e2e call
+def test_resolve_full_size_matches_oracle(be, port):
+    W, H = 1280, 720
+    setup(be, scenes.simple_scene(W, H), W, H)
+    be.render(3, 50, seed=8)
+    acc = be.readback_accum()
+    mean, u8 = port.resolve_fixed(acc[..., :3].copy(), 3)
+    assert_bits_equal(be.readback_f32(), mean, "mean")
+    got = be.readback_rgb8()
+    assert (got != u8).mean() < 1e-6                     # double pow vs glibc powf: no visible difference
+    assert_bits_equal(got, u8, "8-bit")
+
+
+def test_render_frame_equals_staged_calls(be):
+    """rt_render_frame (the cuda_impl-shaped call, host in / host out) == upload + render + readback."""
+    W, H = 200, 120
+    sc = scenes.huge_scene(W, H)
+    img = be.render_frame(sc, W, H, 8, 50, seed=77)
+    setup(be, sc, W, H)
+    be.render(8, 50, seed=77)
+    assert_bits_equal(be.readback_rgb8(), img, "frame")
+    assert img.shape == (H, W, 3) and img[0].mean() > img[-1].mean() * 0.5   # row 0 is the TOP (sky) row
+    sky = img[0].astype(int)
+    assert (sky[:, 2] >= sky[:, 0]).all()                # bluish sky at the top, not the ground
+
+
+# ------------------------------------------------------------------ edge cases and error behaviour
+def test_edge_cases_and_errors(be):
+    from raytracinginoneweekend_b200.backend import Backend
+    sc = scenes.simple_scene(16, 9)
+    fresh = Backend(0)
+    try:
+        with pytest.raises(RtError, match="no scene"):
+            fresh.framebuffer(16, 9) or fresh.render(1)
+        fresh.upload_scene(sc)
+        fresh.framebuffer(16, 9)
+        fresh.render(0)                                  # zero samples: no-op
+        fresh.render(1, tile=(3, 3, 0, 0))               # empty tile: no-op
+        assert fresh.readback_accum().sum() == 0
+        with pytest.raises(RtError, match="outside"):
+            fresh.render(1, tile=(10, 0, 16, 9))
+        with pytest.raises(RtError, match="max_depth"):
+            fresh.render(1, max_depth=0)
+        with pytest.raises(RtError, match="both"):
+            fresh.render(1, flags=FLAG_BRUTE | FLAG_LBVH)
+        fresh.render(1, tile=(15, 8, 1, 1))              # a single pixel
+        acc = fresh.readback_accum()
+        assert acc[8, 15, 3] == 1 and acc[..., 3].sum() == 1
+    finally:
+        fresh.close()
