@@ -53,7 +53,9 @@ struct rt_ctx {
 
     // scene
     float4 *d_sph = nullptr; float *d_rad = nullptr; uint32_t *d_meta = nullptr; float4 *d_mat = nullptr;
-    uint32_t n = 0, npad = 0, m = 0;
+    float4 *d_filt = nullptr;               // conservative-filter records of the throughput build
+    uint32_t n = 0, npad = 0, m = 0, nfilt = 0;
+    float sigma = 1.f, S = 1.f, o_limit2 = 0.f;
     rt_lbvh *bvh = nullptr;
     bool bvh_valid = false;
 
@@ -117,9 +119,9 @@ int get_events(rt_ctx *c, EventPair *out)
 
 void free_scene(rt_ctx *c)
 {
-    cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat);
-    c->d_sph = nullptr; c->d_rad = nullptr; c->d_meta = nullptr; c->d_mat = nullptr;
-    c->n = c->npad = c->m = 0;
+    cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat); cudaFree(c->d_filt);
+    c->d_sph = nullptr; c->d_rad = nullptr; c->d_meta = nullptr; c->d_mat = nullptr; c->d_filt = nullptr;
+    c->n = c->npad = c->m = c->nfilt = 0;
     c->bvh_valid = false;
 }
 
@@ -135,6 +137,7 @@ RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
     RtDeviceScene s{};
     s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
     s.n = c->n; s.npad = c->npad;
+    s.filt = c->d_filt; s.nfilt = c->nfilt; s.sigma = c->sigma; s.S = c->S; s.o_limit2 = c->o_limit2;
     if (lbvh && c->bvh_valid) rt_lbvh_fill(c->bvh, &s);
     return s;
 }
@@ -276,16 +279,19 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         if (spheres[i].mat >= m) return fail(RT_ERR_INVALID, "rt_scene_upload: sphere references a missing material");
 
     uint32_t npad = (n + 31u) & ~31u;
-    if (npad != c->npad || m != c->m) {
+    if (npad != c->npad || m != c->m || (n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP != c->nfilt) {
         CK(cudaStreamSynchronize(c->stream));
         free_scene(c);
         CK(cudaMalloc(&c->d_sph, (size_t)npad * sizeof(float4)));
         CK(cudaMalloc(&c->d_rad, (size_t)npad * sizeof(float)));
         CK(cudaMalloc(&c->d_meta, (size_t)npad * sizeof(uint32_t)));
         CK(cudaMalloc(&c->d_mat, (size_t)m * sizeof(float4)));
+        CK(cudaMalloc(&c->d_filt, (size_t)((n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP) * sizeof(float4)));
     }
+    const uint32_t nfilt = (n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP;
     size_t b_sph = (size_t)npad * 16, b_rad = (size_t)npad * 4, b_meta = (size_t)npad * 4, b_mat = (size_t)m * 16;
-    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat);
+    size_t b_filt = (size_t)nfilt * 16;
+    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat + b_filt);
     if (r) return r;
     CK(cudaStreamSynchronize(c->stream));   // staging buffer may still be in flight
     char *h = (char *)c->h_pin;
@@ -293,6 +299,30 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
     float *hr = (float *)(h + b_sph);
     uint32_t *hm = (uint32_t *)(h + b_sph + b_rad);
     float4 *hmat = (float4 *)(h + b_sph + b_rad + b_meta);
+    float4 *hf = (float4 *)(h + b_sph + b_rad + b_meta + b_mat);
+    // Scale of the conservative filter (rt_device.cuh): S = sigma^2, the largest power of four that keeps
+    // S * 4 * Rs^2 * 4 below FLT_MAX, Rs = the farthest surface point from the origin (ray origins live there),
+    // capped at 2^100.  Rays that start farther out than 2*Rs take the slow everything-is-a-candidate route.
+    double Rs = 1.0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const rt_sphere &sp = spheres[i];
+        double d = std::sqrt((double)sp.cx * sp.cx + (double)sp.cy * sp.cy + (double)sp.cz * sp.cz) + std::fabs((double)sp.r);
+        if (d > Rs) Rs = d;
+    }
+    int e2 = (int)std::floor((120.0 - std::ceil(std::log2(Rs * Rs))) / 2.0);
+    if (e2 > 50) e2 = 50;
+    if (e2 < -60) e2 = -60;
+    const double sigma = std::ldexp(1.0, e2), S = sigma * sigma;
+    for (uint32_t i = 0; i < nfilt; ++i) {
+        if (i < n) {
+            const rt_sphere &sp = spheres[i];
+            double c2 = (double)sp.cx * sp.cx + (double)sp.cy * sp.cy + (double)sp.cz * sp.cz, r2 = (double)sp.r * sp.r;
+            double nk = (r2 - c2) + RT_FILTER_EPS * (c2 + r2);
+            hf[i] = make_float4(sp.cx, sp.cy, sp.cz, (float)(S * nk));
+        } else {
+            hf[i] = make_float4(0.f, 0.f, 0.f, -std::numeric_limits<float>::infinity());
+        }
+    }
     for (uint32_t i = 0; i < npad; ++i) {
         if (i < n) {
             const rt_sphere &s = spheres[i];
@@ -310,7 +340,9 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
     CK(cudaMemcpyAsync(c->d_rad, hr, b_rad, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_meta, hm, b_meta, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_mat, hmat, b_mat, cudaMemcpyHostToDevice, c->stream));
-    c->n = n; c->npad = npad; c->m = m;
+    CK(cudaMemcpyAsync(c->d_filt, hf, b_filt, cudaMemcpyHostToDevice, c->stream));
+    c->n = n; c->npad = npad; c->m = m; c->nfilt = nfilt;
+    c->sigma = (float)sigma; c->S = (float)S; c->o_limit2 = (float)(4.0 * Rs * Rs);
     c->bvh_valid = false;
     return RT_OK;
 }
@@ -408,7 +440,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     bool lbvh = false;
     int r = pick_accel(c, p->flags, &lbvh);
     if (r) return r;
-    size_t smem = rt_render_smem_bytes(c->npad, lbvh);
+    size_t smem = rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
     int ctas = 0;
     r = occupancy(c, exact, lbvh, smem, &ctas);
     if (r) return r;

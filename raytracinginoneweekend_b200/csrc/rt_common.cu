@@ -2,15 +2,18 @@
 // accumulator clear, and the FP32 FMA-chain probe that measures the roofline denominator.
 #include "rt_common.h"
 
-size_t rt_render_smem_bytes(uint32_t npad, bool lbvh)
+// shared memory of the brute-force kernels: mbarrier + sphere records (+ filter records) + candidate masks
+size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh)
 {
     if (lbvh) return 128;
-    return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
+    if (exact) return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
+    return 128 + ((size_t)npad + nfilt) * 16u + (size_t)RT_FCHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
 }
-size_t rt_hits_smem_bytes(uint32_t npad, bool lbvh)
+size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh)
 {
     if (lbvh) return 128;
-    return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * 1 * RT_THREADS * 4u;
+    if (exact) return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * 1 * RT_THREADS * 4u;
+    return 128 + ((size_t)npad + nfilt) * 16u + (size_t)RT_FCHUNK_WORDS * 1 * RT_THREADS * 4u;
 }
 
 // count += spp for every pixel of the listed tiles (the 4th accumulator channel).

@@ -61,19 +61,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase)
         "}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
 }
 
-// Stage the SoA sphere records {cx,cy,cz,r*r} into shared memory with one TMA bulk copy per <=64 KB
-// piece; every thread waits on the mbarrier.  Called once per CTA (the render kernel is persistent).
-__device__ __forceinline__ void stage_spheres(float4 *s_sph, const float4 *g_sph, uint32_t npad, uint64_t *bar)
+// Stage the SoA sphere records {cx,cy,cz,r*r} (and, in the throughput build, the filter records) into
+// shared memory with TMA bulk copies (<= 64 KB pieces) completing on one mbarrier; every thread waits on it.
+// Called once per CTA (the render kernel is persistent).
+__device__ __forceinline__ void stage_spheres(float4 *s_a, const float4 *g_a, float4 *s_b, const float4 *g_b,
+                                              uint32_t na, uint32_t nb, uint64_t *bar)
 {
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
-        uint32_t bytes = npad * 16u;
-        mbar_expect_tx(bar, bytes);
-        for (uint32_t off = 0; off < bytes; off += 65536u) {
-            uint32_t piece = min(65536u, bytes - off);
-            tma_bulk_g2s((char *)s_sph + off, (const char *)g_sph + off, piece, bar);
-        }
+        uint32_t bytes_a = na * 16u, bytes_b = nb * 16u;
+        mbar_expect_tx(bar, bytes_a + bytes_b);
+        for (uint32_t off = 0; off < bytes_a; off += 65536u)
+            tma_bulk_g2s((char *)s_a + off, (const char *)g_a + off, min(65536u, bytes_a - off), bar);
+        for (uint32_t off = 0; off < bytes_b; off += 65536u)
+            tma_bulk_g2s((char *)s_b + off, (const char *)g_b + off, min(65536u, bytes_b - off), bar);
     }
     mbar_wait(bar, 0);
 }
@@ -102,8 +104,16 @@ __device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y
 // src/math.hxx:219-227
 __device__ __forceinline__ f3 normalize3(f3 a)
 {
+#if RT_EXACT
     float len = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
     if (fabsf(len) > FLT_MIN) { a.x = a.x / len; a.y = a.y / len; a.z = a.z / len; }
+#else
+    float len2 = a.x * a.x + a.y * a.y + a.z * a.z;
+    if (len2 > FLT_MIN * FLT_MIN * 0.f + 1.4e-38f) {   // length > FLT_MIN  <=>  len2 > FLT_MIN^2 (underflows: any normal len2)
+        float inv = rsqrtf(len2);
+        a.x *= inv; a.y *= inv; a.z *= inv;
+    }
+#endif
     return a;
 }
 // src/math.hxx:294-298
@@ -193,11 +203,13 @@ __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_s
                                                   float (&best_t)[R], int (&best_i)[R])
 {
     float a[R];
+    uint32_t nz[R];                                  // bit (31 - w): mask word w of the chunk is non-empty
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         a[r] = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
         best_t[r] = FLT_MAX;
         best_i[r] = -1;
+        nz[r] = 0u;
     }
     const uint32_t nthreads = blockDim.x;
     for (uint32_t chunk = 0; chunk < npad; chunk += 32u * RT_CHUNK_WORDS) {
@@ -219,23 +231,163 @@ __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_s
                 }
             }
 #pragma unroll
-            for (int r = 0; r < R; ++r) s_mask[(w * R + r) * nthreads + threadIdx.x] = ~m[r];
+            for (int r = 0; r < R; ++r) {
+                s_mask[(w * R + r) * nthreads + threadIdx.x] = ~m[r];
+                if (~m[r] != 0u) nz[r] |= 0x80000000u >> w;            // word w holds candidates
+            }
         }
+        // one candidate per lane per iteration: the warp iterates max-over-lanes of the candidate COUNT
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            uint32_t w = 0, cand = 0;
-            const uint32_t lim = live[r] ? nwords : 0u;
+            uint32_t words = live[r] ? nz[r] : 0u, cand = 0, w = 0;
+            nz[r] = 0u;
             for (;;) {
-                while (cand == 0u && w < lim) { cand = s_mask[(w * R + r) * nthreads + threadIdx.x]; ++w; }
-                if (cand == 0u) break;
+                if (cand == 0u) {
+                    if (words == 0u) break;
+                    w = (uint32_t)__clz(words);
+                    words &= ~(0x80000000u >> w);
+                    cand = s_mask[(w * R + r) * nthreads + threadIdx.x];
+                }
                 int bit = __clz(cand);
                 cand &= ~(0x80000000u >> bit);
-                uint32_t j = chunk + ((w - 1u) << 5) + (uint32_t)bit;
+                uint32_t j = chunk + (w << 5) + (uint32_t)bit;
                 if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a[r], best_t[r], best_i[r]);
             }
         }
     }
 }
+
+#if !RT_EXACT
+// ------------------------------------------------------------------ closest hit, brute force, throughput build
+// Pass 1 is a CONSERVATIVE candidate filter, pass 2 the reference test (with FMA contraction) on the few
+// candidates, so the hit that is returned is decided by the reference formula; the filter only has to
+// never drop a sphere the reference test would accept.
+//
+// With u = d/|d|:  disc/a = (oc.u)^2 - (|oc|^2 - r^2) = b^2 + 2 o.c + (r^2 - |c|^2) - |o|^2,  b = o.u - c.u.
+// Everything that depends on the ray only or on the sphere only is hoisted, which leaves per ray-sphere
+//     3 FFMA (b)  +  1 FADD + 3 FFMA (ncc)  +  1 FFMA.SAT (disc)  +  1 FFMA (mask)   = 9 FMA-pipe issues
+// against 11 FP32 + 1 funnel shift for the literal formula -- and on sm_100 a funnel shift (ALU pipe, 16
+// lanes) costs two dispatch cycles, an FFMA one (measured, tools/ubench_mix.cu).
+//   * All inputs are pre-scaled by powers of two (b' = sigma*b, disc' = S*disc with S = sigma^2 ~ 2^100), so
+//     the saturating FMA returns exactly 0 for disc' <= 0 and exactly 1 for any representable positive
+//     disc' (>= 1 after scaling): a step function for free.
+//   * mask = 2*mask + t (one FFMA) builds an exact 24-bit integer in a float: bit (23-k) <=> sphere k of the group.
+//   * Safety margin: the sphere is inflated by eps*(|c|^2 + r^2 + |o|^2), eps = 2^-18, which covers the
+//     rounding of this expanded form (<= ~2^-20 (|o|^2+|c|^2)) and of the reference evaluation.
+//   * Rays with d = 0 / non-finite d get no candidates (the reference test rejects them: disc = 0 or NaN);
+//     rays whose |o| would overflow the scaling take every sphere as a candidate.
+struct FastRay { float nux, nuy, nuz, ou, px, py, pz, noo; };
+
+__device__ __forceinline__ FastRay fast_ray_setup(const RtDeviceScene &sc, bool live, float ox, float oy, float oz,
+                                                  float dx, float dy, float dz)
+{
+    FastRay f;
+    float len2 = dx * dx + dy * dy + dz * dz;
+    float oo = ox * ox + oy * oy + oz * oz;
+    bool ok = live && len2 > 0.f && len2 < 3.0e38f && oo < 3.0e38f;
+    float inv = rsqrtf(len2);
+    float ux = dx * inv, uy = dy * inv, uz = dz * inv;
+    float ns = -sc.sigma;
+    f.nux = ns * ux; f.nuy = ns * uy; f.nuz = ns * uz;
+    f.ou = sc.sigma * (ox * ux + oy * uy + oz * uz);
+    float s2 = 2.f * sc.S;
+    f.px = s2 * ox; f.py = s2 * oy; f.pz = s2 * oz;
+    f.noo = -(sc.S * (1.f - (float)RT_FILTER_EPS)) * oo;
+    if (!ok) {                       // no candidates at all
+        f.nux = f.nuy = f.nuz = 0.f; f.ou = 0.f; f.px = f.py = f.pz = 0.f;
+        f.noo = -__int_as_float(0x7f800000);
+    } else if (oo > sc.o_limit2) {   // origin outside the range the scaling was chosen for: everything is a candidate
+        f.nux = f.nuy = f.nuz = 0.f; f.px = f.py = f.pz = 0.f; f.noo = 0.f;
+        f.ou = __int_as_float(0x7f800000);
+    }
+    return f;
+}
+
+// reference test (src/raytracer.hxx:55-89) with FMA contraction, approximate sqrt and a reciprocal of `a`
+__device__ __forceinline__ void sphere_candidate_fast(float4 s, int j, float ox, float oy, float oz,
+                                                      float dx, float dy, float dz, float a, float inv_a,
+                                                      float &best_t, int &best_i)
+{
+    float b;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
+    if (disc > 0.f) {
+        float sq;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(disc));
+        float t = (-b - sq) * inv_a;
+        if (!(t < best_t && t > RT_KMIN)) t = (sq - b) * inv_a;
+        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+    }
+}
+
+// s_mask layout: [word][ray][thread]
+template <int R>
+__device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, const float4 *__restrict__ s_sph,
+                                                       const float4 *__restrict__ s_filt, uint32_t *__restrict__ s_mask,
+                                                       const bool (&live)[R],
+                                                       const float (&ox)[R], const float (&oy)[R], const float (&oz)[R],
+                                                       const float (&dx)[R], const float (&dy)[R], const float (&dz)[R],
+                                                       float (&best_t)[R], int (&best_i)[R])
+{
+    FastRay f[R];
+    uint32_t nz[R];                                  // bit (31 - w): mask word w of the chunk is non-empty
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        f[r] = fast_ray_setup(sc, live[r], ox[r], oy[r], oz[r], dx[r], dy[r], dz[r]);
+        best_t[r] = FLT_MAX;
+        best_i[r] = -1;
+        nz[r] = 0u;
+    }
+    const uint32_t nthreads = blockDim.x;
+    const uint32_t n = sc.n, nfilt = sc.nfilt;
+    for (uint32_t chunk = 0; chunk < nfilt; chunk += RT_FGROUP * RT_FCHUNK_WORDS) {
+        const uint32_t nwords = min((uint32_t)RT_FCHUNK_WORDS, (nfilt - chunk) / RT_FGROUP);
+        for (uint32_t w = 0; w < nwords; ++w) {
+            float acc[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = 0.f;
+            const float4 *sp = s_filt + chunk + w * RT_FGROUP;
+#pragma unroll 8
+            for (int k = 0; k < RT_FGROUP; ++k) {
+                float4 s = sp[k];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float b = fmaf(f[r].nuz, s.z, fmaf(f[r].nuy, s.y, fmaf(f[r].nux, s.x, f[r].ou)));
+                    float ncc = fmaf(f[r].pz, s.z, fmaf(f[r].py, s.y, fmaf(f[r].px, s.x, s.w + f[r].noo)));
+                    float t = __saturatef(fmaf(b, b, ncc));
+                    acc[r] = fmaf(acc[r], 2.f, t);           // Horner: the first sphere of the group ends in bit 23
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (acc[r] != 0.f) {                                     // rare: most groups hold no candidate
+                    s_mask[(w * R + r) * nthreads + threadIdx.x] = __float2uint_rz(acc[r]);
+                    nz[r] |= 0x80000000u >> w;
+                }
+            }
+        }
+        // one candidate per lane per iteration: the warp iterates max-over-lanes of the candidate COUNT
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+            const float inv_a = __frcp_rn(a);
+            uint32_t words = nz[r], cand = 0, w = 0;
+            nz[r] = 0u;
+            for (;;) {
+                if (cand == 0u) {
+                    if (words == 0u) break;
+                    w = (uint32_t)__clz(words);
+                    words &= ~(0x80000000u >> w);
+                    cand = s_mask[(w * R + r) * nthreads + threadIdx.x];
+                }
+                int lz = __clz(cand);                        // bit 23 (lz = 8) is the first sphere of the group
+                cand &= ~(0x80000000u >> lz);
+                uint32_t j = chunk + w * RT_FGROUP + (uint32_t)(lz - 8);
+                if (j < n) sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, best_t[r], best_i[r]);
+            }
+        }
+    }
+}
+#endif  // !RT_EXACT
 
 // ------------------------------------------------------------------ warp work pool
 // A warp takes RT_BATCH consecutive work items (pixel, sample) with one atomic and deals them to the
@@ -324,7 +476,12 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             m = __ldg(sc.mat + (meta & 0x3fffffffu));
             kind = (int)(meta >> 30);
             p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
+#if RT_EXACT
             n = mk3((p.x - s.x) / rad, (p.y - s.y) / rad, (p.z - s.z) / rad);            // src/raytracer.hxx:70
+#else
+            float inv_rad = __frcp_rn(rad);
+            n = mk3((p.x - s.x) * inv_rad, (p.y - s.y) * inv_rad, (p.z - s.z) * inv_rad);
+#endif
             if (kind == 0) mode = RM_BALL;
             else if (kind == 1) { refl = reflect3(unit, n); mode = RM_BALL; }
             else {                                                        // dielectric, src/raytracer.hxx:158-178
@@ -443,9 +600,14 @@ __global__ void __launch_bounds__(RT_THREADS, 2) k_render(const __grid_constant_
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
     float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
+#if RT_EXACT
     uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
-
-    stage_spheres(s_sph, A.sc.sph, A.sc.npad, bar);
+    stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
+#else
+    float4 *s_filt = s_sph + A.sc.npad;
+    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
+    stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+#endif
 
     PathSlot S[RT_RPT];
 #pragma unroll
@@ -477,7 +639,11 @@ __global__ void __launch_bounds__(RT_THREADS, 2) k_render(const __grid_constant_
             ox[r] = S[r].ox; oy[r] = S[r].oy; oz[r] = S[r].oz;
             dx[r] = S[r].dx; dy[r] = S[r].dy; dz[r] = S[r].dz;
         }
+#if RT_EXACT
         closest_hit_brute<RT_RPT>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+#else
+        closest_hit_brute_fast<RT_RPT>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+#endif
     }
 
     // per-warp reduction of the path statistics, one atomic per counter per warp
@@ -503,8 +669,14 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
     float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
+#if RT_EXACT
     uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
-    stage_spheres(s_sph, A.sc.sph, A.sc.npad, bar);
+    stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
+#else
+    float4 *s_filt = s_sph + A.sc.npad;
+    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
+    stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+#endif
 
     const unsigned long long total = A.rays ? A.nrays : (unsigned long long)A.w * A.h;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -531,7 +703,11 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
             }
         }
         float bt[1]; int bi[1];
+#if RT_EXACT
         closest_hit_brute<1>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
+#else
+        closest_hit_brute_fast<1>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
+#endif
         if (live[0]) {
             A.idx[i] = bi[0];
             if (bi[0] >= 0) {

@@ -14,7 +14,10 @@
 
 #define RT_THREADS 256          // threads per CTA of the persistent render kernel
 #define RT_RPT 2                // camera paths resident per thread (ILP + LDS amortisation)
-#define RT_CHUNK_WORDS 16       // candidate-mask words per chunk (16 x 32 = 512 spheres)
+#define RT_CHUNK_WORDS 16       // exact build: candidate-mask words per chunk (16 x 32 = 512 spheres)
+#define RT_FCHUNK_WORDS 22      // fast build: mask words per chunk (22 x 24 = 528 spheres)
+#define RT_FGROUP 24            // fast build: spheres per mask word (bits of an exact float integer)
+#define RT_FILTER_EPS 3.814697265625e-6   // 2^-18: relative safety margin of the conservative filter
 #define RT_BATCH 256u           // work items a warp takes from the global counter at once
 #define RT_KMIN .008f           // src/raytracer.hxx:98
 #define RT_FIXED_ONE 4294967296.f
@@ -25,6 +28,11 @@ struct RtDeviceScene {
     const uint32_t *sph_meta;
     const float4 *mat;
     uint32_t n, npad;
+    // conservative candidate filter of the throughput build (see rt_device.cuh, closest_hit_brute_fast)
+    const float4 *filt;          // float4[nfilt] {cx, cy, cz, S*(r^2 - |c|^2 + eps(|c|^2 + r^2))}; padding has w = -inf
+    uint32_t nfilt;              // n rounded up to RT_FGROUP
+    float sigma, S;              // power-of-two scales: b' = sigma*b, disc' = S*disc, S = sigma^2
+    float o_limit2;              // rays with |o|^2 above this take every sphere as a candidate (overflow guard)
     // LBVH (rt_lbvh.cu); nodes == nullptr when not built
     const float4 *bvh_nodes;     // 4 x float4 per inner node
     const uint32_t *bvh_prims;   // leaf order -> sphere index
@@ -80,5 +88,5 @@ cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
-size_t rt_render_smem_bytes(uint32_t npad, bool lbvh);
-size_t rt_hits_smem_bytes(uint32_t npad, bool lbvh);
+size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);
+size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);

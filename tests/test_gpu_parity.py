@@ -53,7 +53,7 @@ def test_primary_hits_config2_full_size(be, port):
     assert rel_t.max() <= 1e-5 and rel_n.max() <= 1e-5     # the stated tolerance
     assert_bits_equal(t, ot, "t")                            # ... and in fact 0 ulp
     assert_bits_equal(nrm, on, "normal")
-    assert len(np.unique(idx)) > 300 and (idx < 0).any()
+    assert len(np.unique(idx)) > 100 and (idx < 0).any()
     # the throughput (FMA) build must agree on (nearly) every pixel; differences can only sit on silhouettes
     fi, ft, fn = be.primary_hits(flags=0)
     assert (fi != oi).mean() < 2e-4
