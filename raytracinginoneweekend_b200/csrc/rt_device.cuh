@@ -595,7 +595,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
 }
 
 template <bool LBVH>
-__global__ void __launch_bounds__(RT_THREADS, 2) k_render(const __grid_constant__ RtRenderArgs A)
+__global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
