@@ -1,0 +1,31 @@
+// host/cuda_impl.hxx -- the reference-facing entry points of the B200 backend.
+//
+//   void cuda_impl(width, height, image_texels)
+//       EXACTLY the reference's declaration (src/main.cxx:18; defined in src/CUDA/cuda_impl.cu:384-453), so the
+//       reference's main.cxx links against this backend unchanged: the caller owns and pre-sizes the vector
+//       (src/main.cxx:112), the callee fills width*height RGB8 texels in place, row-major, top row first, and
+//       throws std::runtime_error on failure (src/CUDA/cuda_impl.cu:101-114) -- without cudaDeviceReset.
+//       Like the reference's, it renders its own hard-coded scene (src/CUDA/cuda_impl.cu:348-352,404-417) at
+//       the reference GPU path's 48 spp / 32 bounces (src/CUDA/cuda_impl.cu:59-60).
+//
+//   void cuda_impl(width, height, image_texels, data, camera, options)
+//       the same call for a caller-supplied scene (what main() would pass if the scene were not hard-coded).
+#pragma once
+#include <cstdint>
+#include <vector>
+#include "camera.hxx"
+#include "math.hxx"
+#include "raytracer.hxx"
+
+struct cuda_impl_options final {
+    std::uint32_t samples_per_pixel{48};   // src/CUDA/cuda_impl.cu:59
+    std::uint32_t max_depth{32};           // src/CUDA/cuda_impl.cu:60
+    std::uint64_t seed{1};
+    bool exact{false};                     // parity build (no FMA contraction)
+    int device{0};
+};
+
+void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels);
+
+void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels,
+               raytracer::data const &data, raytracer::camera const &camera, cuda_impl_options const &options = {});

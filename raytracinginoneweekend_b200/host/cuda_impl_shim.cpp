@@ -1,0 +1,80 @@
+// host/cuda_impl_shim.cpp -- C++ shim between the reference's interface and the C ABI (include/rt_api.h).
+#include "cuda_impl.hxx"
+
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <variant>
+
+#include "../../include/rt_api.h"
+#include "scenes.hxx"
+
+namespace {
+
+struct ctx_guard final {
+    rt_ctx *ctx{nullptr};
+    ~ctx_guard() { rt_destroy(ctx); }
+};
+
+void check(int rc, char const *what)
+{
+    if (rc != RT_OK) throw std::runtime_error(std::string{what} + ": " + rt_last_error());
+}
+
+}  // namespace
+
+void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels,
+               raytracer::data const &data, raytracer::camera const &camera, cuda_impl_options const &options)
+{
+    if (image_texels.size() != static_cast<std::size_t>(width) * height)
+        throw std::runtime_error("cuda_impl: image_texels must be pre-sized to width*height (src/main.cxx:112)");
+
+    // express the scene with the eye at the origin, where the reference's ray formula is exact
+    auto const eye = camera.position();
+    auto const cam0 = camera.at_origin();
+
+    std::vector<rt_sphere> spheres;
+    spheres.reserve(data.spheres.size());
+    for (auto const &s : data.spheres) {
+        auto c = s.center - eye;
+        spheres.push_back(rt_sphere{c.x, c.y, c.z, s.radius, static_cast<std::uint32_t>(s.material_index)});
+    }
+    std::vector<rt_material> materials;
+    materials.reserve(data.materials.size());
+    for (auto const &m : data.materials) {
+        std::visit([&materials](auto const &mat) {
+            using type = std::decay_t<decltype(mat)>;
+            if constexpr (std::is_same_v<type, material::lambert>)
+                materials.push_back(rt_material{mat.albedo.x, mat.albedo.y, mat.albedo.z, 0.f, RT_LAMBERT});
+            else if constexpr (std::is_same_v<type, material::metal>)
+                materials.push_back(rt_material{mat.albedo.x, mat.albedo.y, mat.albedo.z, mat.roughness, RT_METAL});
+            else
+                materials.push_back(rt_material{mat.albedo.x, mat.albedo.y, mat.albedo.z, mat.refraction_index, RT_DIELECTRIC});
+        }, m);
+    }
+
+    float const cam13[13] = {cam0.position().x, cam0.position().y, cam0.position().z,
+                             cam0.lookat().x, cam0.lookat().y, cam0.lookat().z,
+                             cam0.up().x, cam0.up().y, cam0.up().z,
+                             cam0.aspect(), cam0.vFOV(), cam0.aperture(), cam0.focus_distance()};
+
+    ctx_guard g;
+    check(rt_create(&g.ctx, options.device), "rt_create");
+    rt_render_params p{};
+    p.spp = options.samples_per_pixel;
+    p.max_depth = options.max_depth;
+    p.seed = options.seed;
+    p.sample_base = 0;
+    p.flags = options.exact ? static_cast<std::uint32_t>(RT_FLAG_EXACT) : 0u;
+    static_assert(sizeof(math::u8vec3) == 3, "texels are tightly packed RGB8");
+    check(rt_render_frame(g.ctx, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
+                          static_cast<std::uint32_t>(materials.size()), cam13, width, height, &p,
+                          reinterpret_cast<std::uint8_t *>(image_texels.data())),
+          "rt_render_frame");
+}
+
+void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels)
+{
+    auto const sc = scenes::simple(width, height);
+    cuda_impl(width, height, image_texels, sc.data, sc.camera, cuda_impl_options{});
+}
