@@ -55,7 +55,7 @@ struct rt_ctx {
     float4 *d_sph = nullptr; float *d_rad = nullptr; uint32_t *d_meta = nullptr; float4 *d_mat = nullptr;
     float4 *d_filt = nullptr;               // conservative-filter records of the throughput build
     uint32_t n = 0, npad = 0, m = 0, nfilt = 0;
-    float sigma = 1.f, S = 1.f, o_limit2 = 0.f;
+    float sigma = 1.f, S = 1.f, o_limit2 = 0.f, scene_radius = 1.f;
     rt_lbvh *bvh = nullptr;
     bool bvh_valid = false;
 
@@ -138,7 +138,10 @@ RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
     s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
     s.n = c->n; s.npad = c->npad;
     s.filt = c->d_filt; s.nfilt = c->nfilt; s.sigma = c->sigma; s.S = c->S; s.o_limit2 = c->o_limit2;
-    if (lbvh && c->bvh_valid) rt_lbvh_fill(c->bvh, &s);
+    if (lbvh && c->bvh_valid) {
+        rt_lbvh_fill(c->bvh, &s);
+        s.bvh_pad0 = 16.f * 5.9604644775390625e-8f * c->scene_radius;
+    }
     return s;
 }
 
@@ -151,6 +154,7 @@ int pick_accel(rt_ctx *c, uint32_t flags, bool *lbvh)
     if (!want_bvh && !want_brute) want_bvh = c->n > RT_BRUTE_MAX_SPHERES;
     if (!want_bvh && c->n > RT_BRUTE_MAX_SPHERES)
         return fail(RT_ERR_INVALID, "brute force supports at most RT_BRUTE_MAX_SPHERES spheres (shared-memory staging)");
+    if (want_bvh && c->n < 2) return fail(RT_ERR_INVALID, "the LBVH needs at least 2 spheres");
     if (want_bvh && !c->bvh_valid) {
         if (!c->bvh) { int r = rt_lbvh_create(&c->bvh); if (r) return fail(RT_ERR_CUDA, "rt_lbvh_create failed"); }
         float ms = 0.f; unsigned launches = 0;
@@ -342,7 +346,7 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
     CK(cudaMemcpyAsync(c->d_mat, hmat, b_mat, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_filt, hf, b_filt, cudaMemcpyHostToDevice, c->stream));
     c->n = n; c->npad = npad; c->m = m; c->nfilt = nfilt;
-    c->sigma = (float)sigma; c->S = (float)S; c->o_limit2 = (float)(4.0 * Rs * Rs);
+    c->sigma = (float)sigma; c->S = (float)S; c->o_limit2 = (float)(4.0 * Rs * Rs); c->scene_radius = (float)Rs;
     c->bvh_valid = false;
     return RT_OK;
 }

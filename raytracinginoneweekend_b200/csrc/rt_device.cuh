@@ -389,6 +389,89 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
 }
 #endif  // !RT_EXACT
 
+// ------------------------------------------------------------------ closest hit, LBVH traversal
+// Must return what the brute-force loop returns: the closest t in (kMIN, inf) over ALL spheres, ties to the
+// lowest sphere index.  Two things make that hold in floating point:
+//   * leaves run the reference test per sphere (root selection against FLT_MAX, src/raytracer.hxx:63-89) and
+//     merge with the lexicographic rule (t, index), because leaves arrive in tree order, not index order;
+//   * boxes are tested CONSERVATIVELY.  The float test accepts a ray when dist^2(line, c) < r^2 + E with
+//     E <= ~8 * 2^-24 * |oc|^2, i.e. at a distance up to r + 2^-10.5 |oc|: far spheres are "fatter" for the reference
+//     arithmetic than geometrically.  Each child box is therefore inflated per ray by eta * D + pad0, where
+//     D is the L1 distance from the ray origin to the box's farthest corner (>= |oc| of every sphere in it),
+//     eta = 2^-10, and pad0 covers the rounding of o - c at the scene's scale; the slab interval gets a 1e-5
+//     relative slack.  Culling uses tnear <= best_t (not <), so equal-t candidates with a lower index survive.
+struct BvhCounters { uint32_t nodes, leaves; };
+
+__device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, float ox, float oy, float oz,
+                                         float dx, float dy, float dz, float a, float &best_t, int &best_i, BvhCounters &cnt)
+{
+    uint32_t pos = ref & 0x7fffffffu;
+    float4 s = __ldg(sc.bvh_leaf_sph + pos);
+    int j = (int)__ldg(sc.bvh_prims + pos);
+    ++cnt.leaves;
+    float b;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
+    if (disc > 0.f) {
+        float sq = sqrtf(disc);
+        float t = (-b - sq) / a;
+        bool ok = t < FLT_MAX && t > RT_KMIN;
+        if (!ok) { t = (-b + sq) / a; ok = t < FLT_MAX && t > RT_KMIN; }
+        if (ok && (t < best_t || (t == best_t && j < best_i))) { best_t = t; best_i = j; }
+    }
+}
+
+__device__ __forceinline__ bool bvh_box(float lox, float loy, float loz, float hix, float hiy, float hiz,
+                                        float ox, float oy, float oz, float ix, float iy, float iz,
+                                        float pad0, float best_t, float &tnear)
+{
+    float far = fmaxf(fabsf(ox - lox), fabsf(ox - hix)) + fmaxf(fabsf(oy - loy), fabsf(oy - hiy)) +
+                fmaxf(fabsf(oz - loz), fabsf(oz - hiz));
+    float pad = fmaf(far, 9.765625e-4f, pad0);
+    float t0 = (lox - pad - ox) * ix, t1 = (hix + pad - ox) * ix;
+    float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
+    t0 = (loy - pad - oy) * iy; t1 = (hiy + pad - oy) * iy;
+    tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+    t0 = (loz - pad - oz) * iz; t1 = (hiz + pad - oz) * iz;
+    tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
+    tnear = tn;
+    // relative slack on both ends; a negative tnear (origin inside) passes trivially
+    return tn - fabsf(tn) * 1e-5f <= tf + fabsf(tf) * 1e-5f && tf * 1.00001f >= RT_KMIN && tn - fabsf(tn) * 1e-5f <= best_t;
+}
+
+__device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool live, float ox, float oy, float oz,
+                                                 float dx, float dy, float dz, float &best_t, int &best_i, BvhCounters &cnt)
+{
+    best_t = FLT_MAX;
+    best_i = -1;
+    const float a = dx * dx + dy * dy + dz * dz;
+    if (!live || !(a > 0.f) || !(a < 3.0e38f)) return;      // d = 0 or non-finite: the reference test finds nothing
+    const float ix = 1.f / dx, iy = 1.f / dy, iz = 1.f / dz;
+    uint32_t stack[96];
+    int sp = 0;
+    uint32_t node = sc.bvh_root;
+    for (;;) {
+        const float4 *np = sc.bvh_nodes + 4 * (size_t)node;
+        float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+        ++cnt.nodes;
+        uint32_t left = __float_as_uint(n3.x), right = __float_as_uint(n3.y);
+        float tl, tr;
+        bool hl = bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tl);
+        bool hr = bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tr);
+        if (hl && (left & 0x80000000u)) { bvh_leaf(sc, left, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hl = false; }
+        if (hr && (right & 0x80000000u)) { bvh_leaf(sc, right, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hr = false; }
+        if (hl && hr) {                                       // both inner: near child first, far child on the stack
+            bool left_first = tl <= tr;
+            stack[sp++] = left_first ? right : left;
+            node = left_first ? left : right;
+        } else if (hl) node = left;
+        else if (hr) node = right;
+        else {
+            if (sp == 0) break;
+            node = stack[--sp];
+        }
+    }
+}
+
 // ------------------------------------------------------------------ warp work pool
 // A warp takes RT_BATCH consecutive work items (pixel, sample) with one atomic and deals them to the
 // lanes whose path ended, by ballot + popc prefix -- terminated paths are replaced immediately, so every
@@ -432,7 +515,7 @@ struct PathSlot {
     int st;
 };
 
-struct ThreadStats { uint32_t samples, segments, sky, absorbed, capped; };
+struct ThreadStats { uint32_t samples, segments, sky, absorbed, capped; BvhCounters bvh; };
 
 __device__ __forceinline__ unsigned long long to_fixed(float c)
 {
@@ -442,6 +525,7 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // One shading pass for one path slot: finish the segment just traced (background / material), hand a new
 // camera sample to the slot if its path ended, draw the random numbers every lane needs in ONE shared
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
+template <bool LBVH>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
                                            float best_t, int best_i, WarpPool &pool, ThreadStats &ts)
 {
@@ -470,7 +554,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             ++ts.capped;
             want = true;
         } else {
-            float4 s = s_sph[best_i];
+            float4 s = LBVH ? __ldg(sc.sph + best_i) : s_sph[best_i];
             float rad = __ldg(sc.sph_rad + best_i);
             uint32_t meta = __ldg(sc.sph_meta + best_i);
             m = __ldg(sc.mat + (meta & 0x3fffffffu));
@@ -598,16 +682,22 @@ template <bool LBVH>
 __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
     float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
-#if RT_EXACT
-    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
-    stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
-#else
-    float4 *s_filt = s_sph + A.sc.npad;
-    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
-    stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+    uint32_t *s_mask = nullptr;
+#if !RT_EXACT
+    float4 *s_filt = nullptr;
 #endif
+    if (!LBVH) {
+        uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
+#if RT_EXACT
+        s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
+        stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
+#else
+        s_filt = s_sph + A.sc.npad;
+        s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
+        stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+#endif
+    }
 
     PathSlot S[RT_RPT];
 #pragma unroll
@@ -617,7 +707,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         S[r].ar = S[r].ag = S[r].ab = 1.f;
     }
     WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
-    ThreadStats ts = {0, 0, 0, 0, 0};
+    ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     float best_t[RT_RPT]; int best_i[RT_RPT];
 #pragma unroll
     for (int r = 0; r < RT_RPT; ++r) { best_t[r] = FLT_MAX; best_i[r] = -1; }
@@ -626,30 +716,37 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         bool any_live = false;
 #pragma unroll
         for (int r = 0; r < RT_RPT; ++r) {
-            shade_slot(A, s_sph, S[r], best_t[r], best_i[r], pool, ts);
+            shade_slot<LBVH>(A, s_sph, S[r], best_t[r], best_i[r], pool, ts);
             any_live |= (S[r].st != ST_EMPTY);
         }
         if (!__any_sync(RT_FULL, any_live)) break;
 
-        bool live[RT_RPT];
-        float ox[RT_RPT], oy[RT_RPT], oz[RT_RPT], dx[RT_RPT], dy[RT_RPT], dz[RT_RPT];
+        if (LBVH) {
 #pragma unroll
-        for (int r = 0; r < RT_RPT; ++r) {
-            live[r] = (S[r].st == ST_ACTIVE);
-            ox[r] = S[r].ox; oy[r] = S[r].oy; oz[r] = S[r].oz;
-            dx[r] = S[r].dx; dy[r] = S[r].dy; dz[r] = S[r].dz;
-        }
+            for (int r = 0; r < RT_RPT; ++r)
+                closest_hit_lbvh(A.sc, S[r].st == ST_ACTIVE, S[r].ox, S[r].oy, S[r].oz, S[r].dx, S[r].dy, S[r].dz,
+                                 best_t[r], best_i[r], ts.bvh);
+        } else {
+            bool live[RT_RPT];
+            float ox[RT_RPT], oy[RT_RPT], oz[RT_RPT], dx[RT_RPT], dy[RT_RPT], dz[RT_RPT];
+#pragma unroll
+            for (int r = 0; r < RT_RPT; ++r) {
+                live[r] = (S[r].st == ST_ACTIVE);
+                ox[r] = S[r].ox; oy[r] = S[r].oy; oz[r] = S[r].oz;
+                dx[r] = S[r].dx; dy[r] = S[r].dy; dz[r] = S[r].dz;
+            }
 #if RT_EXACT
-        closest_hit_brute<RT_RPT>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+            closest_hit_brute<RT_RPT>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
 #else
-        closest_hit_brute_fast<RT_RPT>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+            closest_hit_brute_fast<RT_RPT>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
 #endif
+        }
     }
 
     // per-warp reduction of the path statistics, one atomic per counter per warp
-    uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
+    uint32_t v[7] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped, ts.bvh.nodes, ts.bvh.leaves};
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
+    for (int k = 0; k < 7; ++k) {
         uint32_t x = v[k];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
@@ -667,21 +764,27 @@ template <bool LBVH>
 __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtHitArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
     float4 *s_sph = reinterpret_cast<float4 *>(smem_raw + 128);
-#if RT_EXACT
-    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
-    stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
-#else
-    float4 *s_filt = s_sph + A.sc.npad;
-    uint32_t *s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
-    stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+    uint32_t *s_mask = nullptr;
+#if !RT_EXACT
+    float4 *s_filt = nullptr;
 #endif
+    if (!LBVH) {
+        uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw);
+#if RT_EXACT
+        s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + (size_t)A.sc.npad * 16u);
+        stage_spheres(s_sph, A.sc.sph, nullptr, nullptr, A.sc.npad, 0, bar);
+#else
+        s_filt = s_sph + A.sc.npad;
+        s_mask = reinterpret_cast<uint32_t *>(smem_raw + 128 + ((size_t)A.sc.npad + A.sc.nfilt) * 16u);
+        stage_spheres(s_sph, A.sc.sph, s_filt, A.sc.filt, A.sc.npad, A.sc.nfilt, bar);
+#endif
+    }
 
     const unsigned long long total = A.rays ? A.nrays : (unsigned long long)A.w * A.h;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    // every thread runs the same number of iterations: the sphere loop is warp-synchronous
     const unsigned long long iters = (total + stride - 1) / stride;
+    BvhCounters cnt = {0, 0};
     for (unsigned long long it = 0; it < iters; ++it) {
         unsigned long long i = it * stride + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
         bool live[1] = {i < total};
@@ -703,15 +806,19 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
             }
         }
         float bt[1]; int bi[1];
+        if (LBVH) {
+            closest_hit_lbvh(A.sc, live[0], ox[0], oy[0], oz[0], dx[0], dy[0], dz[0], bt[0], bi[0], cnt);
+        } else {
 #if RT_EXACT
-        closest_hit_brute<1>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
+            closest_hit_brute<1>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
 #else
-        closest_hit_brute_fast<1>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
+            closest_hit_brute_fast<1>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
 #endif
+        }
         if (live[0]) {
             A.idx[i] = bi[0];
             if (bi[0] >= 0) {
-                float4 s = s_sph[bi[0]];
+                float4 s = LBVH ? __ldg(A.sc.sph + bi[0]) : s_sph[bi[0]];
                 float rad = __ldg(A.sc.sph_rad + bi[0]);
                 float px = ox[0] + dx[0] * bt[0], py = oy[0] + dy[0] * bt[0], pz = oz[0] + dz[0] * bt[0];
                 A.t[i] = bt[0];
@@ -722,6 +829,16 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
                 A.t[i] = 0.f;
                 A.normal[3 * i + 0] = 0.f; A.normal[3 * i + 1] = 0.f; A.normal[3 * i + 2] = 0.f;
             }
+        }
+    }
+    if (LBVH) {
+        uint32_t v[2] = {cnt.nodes, cnt.leaves};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            uint32_t x = v[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
+            if ((threadIdx.x & 31u) == 0 && x) atomicAdd(A.stats + 5 + k, (unsigned long long)x);
         }
     }
 }

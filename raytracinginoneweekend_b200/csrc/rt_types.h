@@ -36,7 +36,9 @@ struct RtDeviceScene {
     // LBVH (rt_lbvh.cu); nodes == nullptr when not built
     const float4 *bvh_nodes;     // 4 x float4 per inner node
     const uint32_t *bvh_prims;   // leaf order -> sphere index
+    const float4 *bvh_leaf_sph;  // sphere records {cx,cy,cz,r*r} in leaf order
     uint32_t bvh_root;
+    float bvh_pad0;              // absolute box padding (covers the rounding of o - c at the scene's scale)
 };
 
 struct RtDeviceCamera {          // src/camera.hxx:66-76 derived state
