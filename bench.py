@@ -189,6 +189,7 @@ def run_gpu_arm(args):
     from raytracinginoneweekend_b200 import multigpu
     from raytracinginoneweekend_b200.backend import Backend, TileQueue, pack_scene
 
+    os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -218,7 +219,7 @@ def run_gpu_arm(args):
         if world > 1:
             dist.barrier()
 
-    tiles = multigpu.make_tiles(W, H, TILE_W, TILE_H)
+    tiles = multigpu.interleave_tiles(multigpu.make_tiles(W, H, TILE_W, TILE_H), world)
     queue = sched = renderer = None
     if world > 1:
         qname = f"/rtiow_bench_{os.environ.get('MASTER_PORT', '0')}"

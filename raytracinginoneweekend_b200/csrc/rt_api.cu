@@ -473,6 +473,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.tile0 = tile0;
     a.tiles = d_tiles;
     a.TP = (uint32_t)TP;
+    a.TPS = (uint32_t)(TP * p->spp);
     a.spp = p->spp; a.depth = p->max_depth; a.sample_base = p->sample_base;
     a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
     a.stats = c->d_stats;

@@ -592,10 +592,12 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         uint32_t item = pool_take(pool, need, A.work_counter, A.total_items);
         if (need) {
             if (item != 0xffffffffu) {
-                uint32_t s_i = item / A.P;
-                uint32_t q = item - s_i * A.P;
-                uint32_t tl = q / A.TP;
-                uint32_t r = q - tl * A.TP;
+                // item order: tile-major, then sample, then pixel -- a tile's accumulators (TP * 32 B) stay
+                // cache-resident while all of its samples are traced
+                uint32_t tl = item / A.TPS;
+                uint32_t q = item - tl * A.TPS;
+                uint32_t s_i = q / A.TP;
+                uint32_t r = q - s_i * A.TP;
                 uint4 T = A.tiles ? __ldg(A.tiles + A.t0 + tl) : A.tile0;
                 if (r < T.z * T.w) {                                      // edge tiles leave slots unused
                     uint32_t ty = r / T.z;

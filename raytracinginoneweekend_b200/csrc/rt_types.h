@@ -55,11 +55,12 @@ struct RtRenderArgs {
     unsigned long long *accum;   // W*H*4
     uint32_t W, H;               // full image
     // Work domain of one launch: `nt` tiles, each allotted TP = tw*th pixel slots (edge tiles are
-    // smaller and leave slots unused), times spp samples.  item -> (sample, tile, pixel-in-tile).
+    // smaller and leave slots unused), times spp samples.  item -> (tile, sample, pixel-in-tile).
     uint4 tile0;                 // {x0,y0,w,h} when tiles == nullptr (single-tile launch)
     const uint4 *tiles;          // device tile list {x0,y0,w,h} or nullptr
     uint32_t t0;                 // first list entry of this launch
     uint32_t TP;                 // pixel slots per tile (nominal tile width * height)
+    uint32_t TPS;                // TP * spp: work items per tile
     uint32_t P;                  // pixel slots of this launch = nt * TP
     uint32_t spp, depth, sample_base;
     uint32_t key0, key1;

@@ -3,9 +3,10 @@
 The reference has no multi-GPU path; this is new work that BASELINE.json's
 north_star asks for.  Pixels are independent, so the only exchange is the final framebuffer:
 
-* the image is cut into small tiles, tile indices are split into one contiguous range per rank;
+* the image is cut into small tiles; the tile list is interleaved (rank r's range holds every N-th tile, so
+  every range sees the image's cost mix) and split into one contiguous range per rank;
 * every rank owns a cursor (one cache line in POSIX shared memory, ``rt_queue_*``); it takes guided
-  chunks from its own range first (half of what is left, so a rank needs only O(log n) persistent
+  chunks from its own range first (a third of what is left, so a rank needs only O(log n) persistent
   launches) and, when that is dry, steals chunks from the other ranks' cursors -- the path-length
   tail and the sky/glass cost gap make per-tile cost vary by >10x, static splits do not balance;
 * each chunk is ONE ``rt_render_tiles`` launch (a persistent kernel over the tile list); at most
@@ -32,6 +33,15 @@ def make_tiles(W: int, H: int, tw: int, th: int) -> np.ndarray:
             out[k] = (x, y, min(tw, W - x), min(th, H - y))
             k += 1
     return out
+
+
+def interleave_tiles(tiles: np.ndarray, world: int) -> np.ndarray:
+    """Re-order the tile list so that rank r's contiguous range [r*T/N, (r+1)*T/N) holds every N-th tile of the
+    image: each rank's own range then sees the image's cost mix (sky is ~10x cheaper than glass), and stealing
+    only has to fix the residual."""
+    if world <= 1:
+        return tiles
+    return np.concatenate([tiles[r::world] for r in range(world)], axis=0)
 
 
 def rank_ranges(ntiles: int, world: int):
@@ -66,7 +76,7 @@ class StealingScheduler:
         if remaining <= 0:
             return None
         if victim == self.rank:
-            k = max(self.min_chunk, (remaining + 1) // 2)
+            k = max(self.min_chunk, (remaining + 2) // 3)
         else:
             k = max(self.min_chunk, remaining // (2 * self.world))
         start = self.q.next(victim, k)
