@@ -55,7 +55,11 @@ enum { RT_LAMBERT = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
 enum {
     RT_FLAG_EXACT = 1u << 0,      /* parity mode: no FMA contraction, the reference's operation order */
     RT_FLAG_ACCEL_BRUTE = 1u << 1,/* force brute-force closest hit (spheres staged in shared memory) */
-    RT_FLAG_ACCEL_LBVH = 1u << 2  /* force the GPU-built LBVH */
+    RT_FLAG_ACCEL_LBVH = 1u << 2, /* force the GPU-built LBVH */
+    RT_FLAG_FILTER_FMA = 1u << 3  /* brute force, throughput build: run the candidate filter on the FP32 FMA pipe instead of
+                                     the tensor cores (tcgen05 TF32x3 product, the default up to 1024 spheres); same image */,
+    RT_FLAG_FILTER_CHECK = 1u << 4/* self-check: after the filtered closest hit, run the candidate test over ALL spheres and count
+                                     the segments whose result differs in rt_stats.filter_misses (must stay 0; slow) */
     /* neither accel flag: brute force up to RT_BRUTE_MAX_SPHERES, LBVH above */
 };
 #define RT_BRUTE_MAX_SPHERES 8192u
@@ -90,6 +94,7 @@ typedef struct rt_stats {
     double render_ms;      /* device time of the render kernels (CUDA events), cumulative */
     double last_render_ms; /* device time of the most recent rt_render */
     double bvh_build_ms;   /* device time of the most recent LBVH build */
+    uint64_t filter_misses;/* RT_FLAG_FILTER_CHECK: segments where the filtered closest hit differs from the unfiltered one */
 } rt_stats;
 
 RT_EXPORT const char *rt_last_error(void);

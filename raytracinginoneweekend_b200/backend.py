@@ -17,6 +17,8 @@ LIB_PATH = os.path.join(HERE, "librtiow_b200.so")
 FLAG_EXACT = 1 << 0
 FLAG_BRUTE = 1 << 1
 FLAG_LBVH = 1 << 2
+FLAG_FILTER_CHECK = 1 << 4  # count segments whose filtered closest hit differs from the unfiltered one (stats: filter_misses)
+FLAG_FILTER_FMA = 1 << 3   # throughput build: candidate filter on the FMA pipe instead of the tensor cores
 
 EXPORTS = [
     "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync", "rt_throttle",
@@ -50,7 +52,7 @@ class RtStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("segments", C.c_uint64), ("sphere_tests", C.c_uint64),
                 ("node_visits", C.c_uint64), ("sky", C.c_uint64), ("absorbed", C.c_uint64),
                 ("capped", C.c_uint64), ("launches", C.c_uint64), ("render_ms", C.c_double),
-                ("last_render_ms", C.c_double), ("bvh_build_ms", C.c_double)]
+                ("last_render_ms", C.c_double), ("bvh_build_ms", C.c_double), ("filter_misses", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

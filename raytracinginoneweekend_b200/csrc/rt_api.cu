@@ -2,6 +2,7 @@
 // readback, statistics, PPM writer, FP32 probe and the node-level tile queue.
 // Host code only (compiled with -Xcompiler -ffp-contract=off so the camera maths keeps the reference's
 // float rounding); all device work is in rt_kernels_{exact,fast}.cu, rt_common.cu and rt_lbvh.cu.
+#include <algorithm>
 #include <atomic>
 #include <cerrno>
 #include <cfloat>
@@ -54,6 +55,9 @@ struct rt_ctx {
     // scene
     float4 *d_sph = nullptr; float *d_rad = nullptr; uint32_t *d_meta = nullptr; float4 *d_mat = nullptr;
     float4 *d_filt = nullptr;               // conservative-filter records of the throughput build
+    float4 *d_tcb = nullptr;                // tensor-filter sphere matrix (rt_tensor.cuh), nullptr above RT_TC_MAX_SPHERES
+    uint32_t tc_ns = 0;
+    float tc_g[3] = {0.f, 0.f, 0.f};
     uint32_t n = 0, npad = 0, m = 0, nfilt = 0;
     float sigma = 1.f, S = 1.f, o_limit2 = 0.f, scene_radius = 1.f;
     rt_lbvh *bvh = nullptr;
@@ -119,7 +123,8 @@ int get_events(rt_ctx *c, EventPair *out)
 
 void free_scene(rt_ctx *c)
 {
-    cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat); cudaFree(c->d_filt);
+    cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat); cudaFree(c->d_filt); cudaFree(c->d_tcb);
+    c->d_tcb = nullptr; c->tc_ns = 0;
     c->d_sph = nullptr; c->d_rad = nullptr; c->d_meta = nullptr; c->d_mat = nullptr; c->d_filt = nullptr;
     c->n = c->npad = c->m = c->nfilt = 0;
     c->bvh_valid = false;
@@ -138,6 +143,8 @@ RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
     s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
     s.n = c->n; s.npad = c->npad;
     s.filt = c->d_filt; s.nfilt = c->nfilt; s.sigma = c->sigma; s.S = c->S; s.o_limit2 = c->o_limit2;
+    s.tc_b = c->d_tcb; s.tc_ns = c->tc_ns; s.tc_gx = c->tc_g[0]; s.tc_gy = c->tc_g[1]; s.tc_gz = c->tc_g[2];
+    s.tc_eps = (float)RT_TC_EPS;
     if (lbvh && c->bvh_valid) {
         rt_lbvh_fill(c->bvh, &s);
         s.bvh_pad0 = 16.f * 5.9604644775390625e-8f * c->scene_radius;
@@ -293,9 +300,16 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         CK(cudaMalloc(&c->d_filt, (size_t)((n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP) * sizeof(float4)));
     }
     const uint32_t nfilt = (n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP;
+    const uint32_t tc_ns = (n <= RT_TC_MAX_SPHERES) ? (n + 127u) / 128u * 128u : 0u;
+    if (tc_ns != c->tc_ns || (tc_ns && !c->d_tcb)) {
+        CK(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_tcb); c->d_tcb = nullptr; c->tc_ns = 0;
+        if (tc_ns) CK(cudaMalloc(&c->d_tcb, (size_t)tc_ns * 8 * sizeof(float4)));
+        c->tc_ns = tc_ns;
+    }
     size_t b_sph = (size_t)npad * 16, b_rad = (size_t)npad * 4, b_meta = (size_t)npad * 4, b_mat = (size_t)m * 16;
-    size_t b_filt = (size_t)nfilt * 16;
-    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat + b_filt);
+    size_t b_filt = (size_t)nfilt * 16, b_tcb = (size_t)tc_ns * 8 * 16;
+    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat + b_filt + b_tcb);
     if (r) return r;
     CK(cudaStreamSynchronize(c->stream));   // staging buffer may still be in flight
     char *h = (char *)c->h_pin;
@@ -340,6 +354,48 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         }
     }
     for (uint32_t i = 0; i < m; ++i) hmat[i] = make_float4(materials[i].r, materials[i].g, materials[i].b, materials[i].param);
+    if (tc_ns) {
+        // Sphere side of the bilinear form of rt_tensor.cuh, expanded about g = the component-wise median of the
+        // centres (keeps |c - g| small for the many small spheres whatever the ground sphere does).
+        // Slots: 9 terms {xx,yy,zz,xy,xz,yz,x,y,z} x (f_h, f_l, f_h) | w_h, w_m, w_l | 1, 1 with
+        // w = r^2 - |c|^2 + eps (|c|^2 + r^2); hi parts are TF32 (10-bit mantissa, round to nearest), evaluated in double.
+        // Column pos = 32 b + v holds sphere 32 b + 7 + 8 (v & 3) - (v >> 2): the sign-mask bit order (tc::sign_mask).
+        float *hb = (float *)(h + b_sph + b_rad + b_meta + b_mat + b_filt);
+        std::memset(hb, 0, b_tcb);
+        std::vector<float> med(n);
+        float g[3];
+        for (int ax = 0; ax < 3; ++ax) {
+            for (uint32_t i = 0; i < n; ++i) med[i] = ax == 0 ? spheres[i].cx : ax == 1 ? spheres[i].cy : spheres[i].cz;
+            std::nth_element(med.begin(), med.begin() + n / 2, med.end());
+            g[ax] = std::isfinite(med[n / 2]) ? med[n / 2] : 0.f;
+        }
+        auto tf32 = [](double x) {
+            float f = (float)x; uint32_t u; std::memcpy(&u, &f, 4);
+            if ((u & 0x7f800000u) == 0x7f800000u) return f;
+            u += 0x1000u; u &= 0xffffe000u; std::memcpy(&f, &u, 4); return f;
+        };
+        auto put = [&](uint32_t pos, uint32_t slot, float v) { hb[((size_t)(slot >> 2) * tc_ns + pos) * 4 + (slot & 3u)] = v; };
+        for (uint32_t pos = 0; pos < tc_ns; ++pos) {
+            const uint32_t v = pos & 31u, i = (pos & ~31u) + 7u + 8u * (v & 3u) - (v >> 2);
+            if (i >= n) { put(pos, 27, -3.0e38f); continue; }           // padding: never a candidate
+            const rt_sphere &sp = spheres[i];
+            const double x = (double)sp.cx - g[0], y = (double)sp.cy - g[1], z = (double)sp.cz - g[2], r2 = (double)sp.r * sp.r;
+            const double f[9] = {x * x, y * y, z * z, x * y, x * z, y * z, x, y, z};
+            for (uint32_t t = 0; t < 9; ++t) {
+                float fh = tf32(f[t]);
+                float fl = (float)(f[t] - (double)fh);
+                put(pos, 3 * t + 0, fh); put(pos, 3 * t + 1, fl); put(pos, 3 * t + 2, fh);
+            }
+            const double c2 = x * x + y * y + z * z;
+            const double w = (r2 - c2) + RT_TC_EPS * (c2 + r2);
+            float wh = tf32(w), wm = tf32(w - (double)wh);
+            float wl = (float)(w - (double)wh - (double)wm);
+            put(pos, 27, wh); put(pos, 28, wm); put(pos, 29, wl);
+            put(pos, 30, 1.f); put(pos, 31, 1.f);
+        }
+        CK(cudaMemcpyAsync(c->d_tcb, hb, b_tcb, cudaMemcpyHostToDevice, c->stream));
+        c->tc_g[0] = g[0]; c->tc_g[1] = g[1]; c->tc_g[2] = g[2];
+    }
     CK(cudaMemcpyAsync(c->d_sph, hs, b_sph, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_rad, hr, b_rad, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_meta, hm, b_meta, cudaMemcpyHostToDevice, c->stream));
@@ -444,10 +500,16 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     bool lbvh = false;
     int r = pick_accel(c, p->flags, &lbvh);
     if (r) return r;
-    size_t smem = rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
-    int ctas = 0;
-    r = occupancy(c, exact, lbvh, smem, &ctas);
-    if (r) return r;
+    // throughput build, brute force: the candidate filter runs on the tensor cores unless the scene is too large
+    // for the shared-memory sphere matrix or the caller asks for the FMA-pipe filter
+    // (below RT_TC_MIN_SPHERES one 128-column tile is mostly padding and the FMA-pipe loop is shorter than the handshake)
+    const bool tensor = !exact && !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(p->flags & RT_FLAG_FILTER_FMA);
+    size_t smem = tensor ? rt_render_tc_smem_bytes(c->npad, c->tc_ns) : rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
+    int ctas = 1;                      // the tensor kernel owns the SM (all 512 TMEM columns): one CTA per SM
+    if (!tensor) {
+        r = occupancy(c, exact, lbvh, smem, &ctas);
+        if (r) return r;
+    }
 
     EventPair ev;
     r = get_events(c, &ev);
@@ -477,6 +539,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.spp = p->spp; a.depth = p->max_depth; a.sample_base = p->sample_base;
     a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
     a.stats = c->d_stats;
+    a.check = (p->flags & RT_FLAG_FILTER_CHECK) ? 1u : 0u;
 
     // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic)
     uint32_t per_band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);
@@ -490,12 +553,14 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
             c->counter_slot = 0;
         }
         a.work_counter = c->d_counter + c->counter_slot++;
-        unsigned long long want_ctas = (a.total_items + (unsigned long long)RT_THREADS * RT_RPT - 1) / ((unsigned long long)RT_THREADS * RT_RPT);
+        const unsigned long long per_cta = tensor ? 384ull : (unsigned long long)RT_THREADS * RT_RPT;
+        unsigned long long want_ctas = (a.total_items + per_cta - 1) / per_cta;
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
-        cudaError_t e = exact ? rtx::launch_render(a, grid, smem, c->stream, lbvh)
-                              : rtf::launch_render(a, grid, smem, c->stream, lbvh);
+        cudaError_t e = tensor ? rtf::launch_render_tc(a, grid, smem, c->stream)
+                        : exact ? rtx::launch_render(a, grid, smem, c->stream, lbvh)
+                                : rtf::launch_render(a, grid, smem, c->stream, lbvh);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
     }
@@ -686,6 +751,7 @@ int rt_stats_get(rt_ctx *c, rt_stats *out)
     out->samples = h[0]; out->segments = h[1]; out->sky = h[2]; out->absorbed = h[3]; out->capped = h[4];
     out->node_visits = h[5];
     out->sphere_tests = h[6];
+    out->filter_misses = h[7];
     return RT_OK;
 }
 

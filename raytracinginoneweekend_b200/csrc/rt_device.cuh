@@ -680,7 +680,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     }
 }
 
-template <bool LBVH>
+template <bool LBVH, bool CHECK = false>
 __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -741,6 +741,18 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
             closest_hit_brute<RT_RPT>(s_sph, A.sc.n, A.sc.npad, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
 #else
             closest_hit_brute_fast<RT_RPT>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, best_t, best_i);
+            if (CHECK) {                            // RT_FLAG_FILTER_CHECK: the same test over all spheres must agree
+#pragma unroll
+                for (int r = 0; r < RT_RPT; ++r) {
+                    if (!live[r]) continue;
+                    const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+                    const float inv_a = __frcp_rn(a);
+                    float ct = FLT_MAX; int ci = -1;
+                    for (uint32_t j = 0; j < A.sc.n; ++j)
+                        sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, ct, ci);
+                    if (ci != best_i[r] || ct != best_t[r]) atomicAdd(A.stats + 7, 1ull);
+                }
+            }
 #endif
         }
     }
@@ -758,6 +770,10 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         }
     }
 }
+
+#if !RT_EXACT
+#include "rt_tensor.cuh"
+#endif
 
 // ------------------------------------------------------------------ parity pass: primary / caller-supplied rays
 // One thread per ray; the same two-pass brute-force closest hit.  Primary rays: u = x/W, v = y/H, lens

@@ -1,0 +1,309 @@
+// rt_tensor.cuh -- brute-force closest hit with the candidate filter on the 5th-generation tensor cores.
+// Included by rt_device.cuh in the throughput build only (namespace rtf).
+//
+// What is computed.  For a ray (o, u = d/|d|) and a sphere (c, r) the sign of the discriminant of
+// src/raytracer.hxx:55-61 is the sign of
+//     q = (u.(c-o))^2 - |c-o|^2 + r^2
+//       = sum_ij u_i u_j c_i c_j  +  p.c  +  (r^2 - |c|^2)  +  k,      p = 2(o - (u.o)u),  k = -|o - (u.o)u|^2,
+// a BILINEAR form: (ray features) x (sphere features).  One pass of 128 rays over N spheres is therefore a
+// [128 x K] x [K x N] matrix product.  It runs as tcgen05.mma kind::tf32 with FP32-accurate inputs through 3-way
+// split products (a_h f_h + a_h f_l + a_l f_h, |a_l| <= 2^-11 |a|): K = 9 terms x 3 + 3 (r^2-|c|^2 in three
+// pieces) + 2 (k in two pieces) = 32.  Accumulators live in TMEM; the ray rows are the A operand, written to
+// TMEM by the thread that owns the ray (tcgen05.st), the sphere matrix is the B operand in shared memory
+// (canonical K-major no-swizzle layout, staged once per CTA by TMA).
+//
+// The product is only a CONSERVATIVE FILTER, exactly like the FMA-pipe filter it replaces: the sphere is
+// inflated by eps (|c|^2 + r^2 + |o|^2), eps = 2^-16 (measured error of q: < 2^-20.4 of that scale,
+// tools/proto_tc.cu), so no sphere the reference test accepts is dropped; the hit that is returned is decided
+// by the reference test (sphere_candidate_fast) on the few candidates, in increasing sphere index.
+//
+// Per SM: ONE CTA = 3 ray warpgroups (128 rays each, one ray per thread = one TMEM lane) + 3 MMA-issuer warps.
+// TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + 128 columns of accumulators (D).
+// Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full (tcgen05.commit) -> ray warps;
+// empty (accumulators copied to registers) -> issuer.  A chunk is 128 spheres = 4 MMAs (M128 N128 K8).
+// Epilogue: tcgen05.ld 32 columns -> 32 registers -> sign mask with 16 I2IP (two saturating s32->u8 packs per
+// op) + 8 LOP3 -> the non-empty mask words go to shared memory -> pass 2 as in the FMA-pipe build.
+#pragma once
+
+#define RT_TC_WGS 3                       // ray warpgroups per CTA
+#define RT_TC_RAY_THREADS (RT_TC_WGS * 128)
+#define RT_TC_THREADS (RT_TC_RAY_THREADS + RT_TC_WGS * 32)
+#define RT_TC_CHUNK 128                   // spheres per accumulator tile
+#define RT_TC_KQ 8                        // K = 32 tf32 slots = 8 chunks of 16 bytes
+#define RT_TC_WGCOLS (32 + RT_TC_CHUNK)   // TMEM columns per warpgroup
+
+namespace tc {
+
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    // K-major, SWIZZLE_NONE: core matrix = 8 rows x 16 B contiguous; LBO = distance between the two 16-byte
+    // k-chunks of one K=8 step, SBO = distance between 8-row groups; bit 46 = descriptor version (sm_100)
+    return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T, M = 128, N = RT_TC_CHUNK, K = 8 (tf32), issued by ONE thread
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void bar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n.reg .pred P1;\nTC_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra TC_DONE;\nbra TC_WAIT;\nTC_DONE:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// warpgroup-wide OR over a named barrier (ids 1..RT_TC_WGS)
+__device__ __forceinline__ bool wg_any(uint32_t id, bool pred)
+{
+    uint32_t r;
+    asm volatile("{\n.reg .pred p, q;\nsetp.ne.u32 q, %1, 0;\nbar.red.or.pred p, %2, 128, q;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(r) : "r"((uint32_t)pred), "r"(id) : "memory");
+    return r != 0u;
+}
+__device__ __forceinline__ float tf32_round(float x)
+{
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+#define RT_TC_LD32(v, addr)                                                                                               \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                \
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27," \
+                 "%28,%29,%30,%31}, [%32];"                                                                               \
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),        \
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),  \
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]),             \
+                   "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]),             \
+                   "=r"(v[30]), "=r"(v[31])                                                                               \
+                 : "r"(addr))
+#define RT_TC_ST32(addr, v)                                                                                               \
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "                                                          \
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28," \
+                 "%29,%30,%31,%32};"                                                                                      \
+                 ::"r"(addr), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]),     \
+                   "f"(v[8]), "f"(v[9]), "f"(v[10]), "f"(v[11]), "f"(v[12]), "f"(v[13]), "f"(v[14]), "f"(v[15]),          \
+                   "f"(v[16]), "f"(v[17]), "f"(v[18]), "f"(v[19]), "f"(v[20]), "f"(v[21]), "f"(v[22]), "f"(v[23]),        \
+                   "f"(v[24]), "f"(v[25]), "f"(v[26]), "f"(v[27]), "f"(v[28]), "f"(v[29]), "f"(v[30]), "f"(v[31])         \
+                 : "memory")
+
+// Sign mask of 32 accumulator words: bit (8p + j) <=> word 4j + 3 - p is a positive float.  The host places
+// sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2), so that __clz order = sphere order.
+__device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
+{
+    uint32_t m = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        uint32_t t, w;
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[4 * j + 0]), "r"(v[4 * j + 1]), "r"(0u));
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(w) : "r"(v[4 * j + 2]), "r"(v[4 * j + 3]), "r"(t));
+        m |= w & (0x01010101u << j);
+    }
+    return m;
+}
+
+// Ray -> the 32 A-operand slots (slot order must match tc_sphere_row on the host, rt_api.cu)
+__device__ __forceinline__ void ray_row(const RtDeviceScene &sc, bool live, float ox, float oy, float oz,
+                                        float dx, float dy, float dz, float (&row)[32])
+{
+    ox -= sc.tc_gx; oy -= sc.tc_gy; oz -= sc.tc_gz;
+    float len2 = dx * dx + dy * dy + dz * dz;
+    float oo = ox * ox + oy * oy + oz * oz;
+    bool ok = live && len2 > 0.f && len2 < 3.0e38f && oo < 1.0e30f;
+    float inv = rsqrtf(len2);
+    float ux = dx * inv, uy = dy * inv, uz = dz * inv;
+    float uo = ux * ox + uy * oy + uz * oz;
+    float qx = ox - uo * ux, qy = oy - uo * uy, qz = oz - uo * uz;
+    float kk = fmaf(sc.tc_eps, oo, -(qx * qx + qy * qy + qz * qz));
+    float co[9] = {ux * ux, uy * uy, uz * uz, 2.f * ux * uy, 2.f * ux * uz, 2.f * uy * uz, 2.f * qx, 2.f * qy, 2.f * qz};
+    if (!ok) {                              // no candidates: d = 0 / non-finite ray (the reference test rejects it), idle slot
+#pragma unroll
+        for (int t = 0; t < 9; ++t) co[t] = 0.f;
+        kk = -3.0e38f;
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+        float h = tf32_round(co[t]);
+        row[3 * t + 0] = h; row[3 * t + 1] = h; row[3 * t + 2] = co[t] - h;
+    }
+    row[27] = 1.f; row[28] = 1.f; row[29] = 1.f;
+    float h = tf32_round(kk);
+    row[30] = h; row[31] = kk - h;
+}
+
+}  // namespace tc
+
+// shared memory: [0,128) barriers + TMEM base + done flags | B matrix | sphere records | candidate mask words
+//   bars[0] staging; per warpgroup w: bars[1+3w] a_ready (4 arrivals), [2+3w] full (1), [3+3w] empty (4)
+__global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_constant__ RtRenderArgs A)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem_raw + 96);
+    volatile uint32_t *s_done = reinterpret_cast<volatile uint32_t *>(smem_raw + 100);
+    const uint32_t ns = A.sc.tc_ns, npad = A.sc.npad, n = A.sc.n;
+    float4 *s_b = reinterpret_cast<float4 *>(smem_raw + 128);
+    float4 *s_sph = s_b + (size_t)ns * RT_TC_KQ;
+    uint32_t *s_mask = reinterpret_cast<uint32_t *>(s_sph + npad);
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t nch = ns / RT_TC_CHUNK;
+
+    if (tid == 0) {
+        for (int w = 0; w < RT_TC_WGS; ++w) {
+            tc::bar_init(bars + 1 + 3 * w, 4); tc::bar_init(bars + 2 + 3 * w, 1); tc::bar_init(bars + 3 + 3 * w, 4);
+            s_done[w] = 0u;
+        }
+    }
+    stage_spheres(s_sph, A.sc.sph, s_b, A.sc.tc_b, npad, ns * RT_TC_KQ, bars);      // inits bars[0], fences, TMA, wait
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(s_tmem)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc::fence_before();
+    __syncthreads();
+    tc::fence_after();
+    const uint32_t tmem_base = *s_tmem;
+
+    if (warp >= RT_TC_WGS * 4) {
+        // ============================================================ MMA issuer: one thread per warpgroup
+        const uint32_t w = warp - RT_TC_WGS * 4;
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(RT_TC_CHUNK >> 3) << 17) | ((128u >> 4) << 24);
+            const uint64_t bdesc0 = tc::smem_desc(smem_u32(s_b), ns * 16u, 128u);
+            uint64_t *bar = bars + 1 + 3 * w;
+            const uint32_t tmem_a = tmem_base + w * RT_TC_WGCOLS, tmem_d = tmem_a + 32;
+            uint32_t uses = 0;
+            for (uint32_t pass = 0;; ++pass) {
+                tc::bar_wait(bar + 0, pass & 1u);                                   // ray rows are in TMEM
+                if (s_done[w]) break;
+                for (uint32_t c = 0; c < nch; ++c) {
+                    if (uses >= 1u) tc::bar_wait(bar + 2, (uses - 1u) & 1u);         // accumulators consumed
+                    tc::fence_after();
+#pragma unroll
+                    for (uint32_t ks = 0; ks < RT_TC_KQ / 2; ++ks) {
+                        // K step = 2 k-chunks (2 * ns * 16 bytes apart in s_b); chunk c starts at row 128 c
+                        uint64_t bd = bdesc0 + (uint64_t)(((ks * 2u * ns + c * RT_TC_CHUNK) * 16u) >> 4);
+                        tc::mma_tf32_ts(tmem_d, tmem_a + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
+                    }
+                    tc::mma_commit(bar + 1);
+                    ++uses;
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ============================================================ ray warps: one path per thread
+        const uint32_t wg = warp >> 2;
+        const uint32_t lane_off = ((warp & 3u) * 32u) << 16;
+        const uint32_t tmem_a = tmem_base + wg * RT_TC_WGCOLS + lane_off, tmem_d = tmem_a + 32;
+        uint64_t *bar = bars + 1 + 3 * wg;
+        uint32_t full_parity = 0;
+
+        PathSlot S;
+        S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
+        S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
+        S.ar = S.ag = S.ab = 1.f;
+        WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+        ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
+        float best_t = FLT_MAX; int best_i = -1;
+
+        for (;;) {
+            shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts);
+            const bool live = (S.st == ST_ACTIVE);
+            if (!tc::wg_any(1u + wg, S.st != ST_EMPTY)) {                           // whole warpgroup out of work
+                if ((tid & 127u) == 0u) s_done[wg] = 1u;
+                __syncwarp();
+                if (lane == 0) tc::bar_arrive(bar + 0);
+                break;
+            }
+            {
+                float row[32];
+                tc::ray_row(A.sc, live, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, row);
+                RT_TC_ST32(tmem_a, row);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) tc::bar_arrive(bar + 0);
+            }
+            uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
+            for (uint32_t c = 0; c < nch; ++c) {
+                tc::bar_wait(bar + 1, full_parity);
+                full_parity ^= 1u;
+                tc::fence_after();
+#pragma unroll
+                for (uint32_t h = 0; h < 2; ++h) {
+                    uint32_t v0[32], v1[32];
+                    RT_TC_LD32(v0, tmem_d + h * 64u);
+                    RT_TC_LD32(v1, tmem_d + h * 64u + 32u);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (h == 1u) {                   // all 128 columns are in registers: hand the tile back
+                        tc::fence_before();
+                        __syncwarp();
+                        if (lane == 0) tc::bar_arrive(bar + 2);
+                    }
+                    const uint32_t m0 = tc::sign_mask(v0), m1 = tc::sign_mask(v1);
+                    const uint32_t w0 = c * 4u + h * 2u;
+                    if (m0) { s_mask[w0 * RT_TC_RAY_THREADS + tid] = m0; nz |= 0x80000000u >> w0; }
+                    if (m1) { s_mask[(w0 + 1u) * RT_TC_RAY_THREADS + tid] = m1; nz |= 0x80000000u >> (w0 + 1u); }
+                }
+            }
+            // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
+            best_t = FLT_MAX; best_i = -1;
+            {
+                const float a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+                const float inv_a = __frcp_rn(a);
+                uint32_t words = live ? nz : 0u, cand = 0u, w = 0u;
+                for (;;) {
+                    if (cand == 0u) {
+                        if (words == 0u) break;
+                        w = (uint32_t)__clz(words);
+                        words &= ~(0x80000000u >> w);
+                        cand = s_mask[w * RT_TC_RAY_THREADS + tid];
+                    }
+                    const int lz = __clz(cand);
+                    cand &= ~(0x80000000u >> lz);
+                    const uint32_t j = (w << 5) + (uint32_t)lz;
+                    if (j < n) sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a, best_t, best_i);
+                }
+                if (A.check && live) {              // self-check: the same test over all spheres must agree
+                    float ct = FLT_MAX; int ci = -1;
+                    for (uint32_t j = 0; j < n; ++j)
+                        sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a, ct, ci);
+                    if (ci != best_i || ct != best_t) atomicAdd(A.stats + 7, 1ull);
+                }
+            }
+        }
+
+        uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            uint32_t x = v[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
+            if (lane == 0 && x) {
+                atomicAdd(A.stats + k, (unsigned long long)x);
+                if (k == 1) atomicAdd(A.stats + 6, (unsigned long long)x * n);
+            }
+        }
+    }
+    tc::fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
+}

@@ -33,6 +33,11 @@ struct RtDeviceScene {
     uint32_t nfilt;              // n rounded up to RT_FGROUP
     float sigma, S;              // power-of-two scales: b' = sigma*b, disc' = S*disc, S = sigma^2
     float o_limit2;              // rays with |o|^2 above this take every sphere as a candidate (overflow guard)
+    // tensor-core candidate filter of the throughput build (rt_tensor.cuh); tc_b == nullptr when the scene is too large
+    const float4 *tc_b;          // float4[8][tc_ns]: sphere feature matrix, K-major core-matrix layout, permuted columns
+    uint32_t tc_ns;              // n rounded up to 128 (accumulator tile width)
+    float tc_gx, tc_gy, tc_gz;   // centre the bilinear form is expanded about
+    float tc_eps;                // relative inflation of the filter (2^-16)
     // LBVH (rt_lbvh.cu); nodes == nullptr when not built
     const float4 *bvh_nodes;     // 4 x float4 per inner node
     const uint32_t *bvh_prims;   // leaf order -> sphere index
@@ -66,7 +71,8 @@ struct RtRenderArgs {
     uint32_t key0, key1;
     uint32_t total_items;        // P * spp  (< 2^31)
     uint32_t *work_counter;      // zeroed before launch
-    unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] sphere tests
+    unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] sphere tests [7] filter misses
+    uint32_t check;              // RT_FLAG_FILTER_CHECK
 };
 
 struct RtHitArgs {
@@ -91,5 +97,12 @@ cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
+namespace rtf {
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
+}
+#define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
+#define RT_TC_MIN_SPHERES 48u
+#define RT_TC_MAX_SPHERES 1024u   // tensor-filter path: B matrix (128 B per sphere) + records + masks fit in shared memory
+size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns);
 size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);
 size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);

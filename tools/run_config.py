@@ -2,14 +2,14 @@
 import os, sys, time, json, argparse
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from raytracinginoneweekend_b200 import scenes
-from raytracinginoneweekend_b200.backend import Backend, FLAG_EXACT, FLAG_LBVH, FLAG_BRUTE, write_ppm
+from raytracinginoneweekend_b200.backend import Backend, FLAG_EXACT, FLAG_LBVH, FLAG_BRUTE, FLAG_FILTER_FMA, write_ppm
 ap = argparse.ArgumentParser()
 ap.add_argument("--scene", default="huge"); ap.add_argument("--width", type=int, default=1280); ap.add_argument("--height", type=int, default=720)
 ap.add_argument("--spp", type=int, default=16); ap.add_argument("--depth", type=int, default=50); ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--exact", action="store_true"); ap.add_argument("--lbvh", action="store_true"); ap.add_argument("--brute", action="store_true")
-ap.add_argument("--out", default="")
+ap.add_argument("--fma", action="store_true"); ap.add_argument("--out", default="")
 a = ap.parse_args()
-flags = (FLAG_EXACT if a.exact else 0) | (FLAG_LBVH if a.lbvh else 0) | (FLAG_BRUTE if a.brute else 0)
+flags = (FLAG_EXACT if a.exact else 0) | (FLAG_LBVH if a.lbvh else 0) | (FLAG_BRUTE if a.brute else 0) | (FLAG_FILTER_FMA if a.fma else 0)
 t0 = time.time(); sc = scenes.get_scene(a.scene, a.width, a.height); t1 = time.time()
 be = Backend(0); be.upload_scene(sc); be.framebuffer(a.width, a.height)
 for i in range(a.reps):
