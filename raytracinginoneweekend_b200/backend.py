@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librtiow_b200.so")
+LIB_PATH = os.environ.get("RTIOW_LIB") or os.path.join(HERE, "librtiow_b200.so")   # RTIOW_LIB: experimental variant builds (tools/build_variant.sh)
 
 FLAG_EXACT = 1 << 0
 FLAG_BRUTE = 1 << 1

@@ -300,7 +300,8 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         CK(cudaMalloc(&c->d_filt, (size_t)((n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP) * sizeof(float4)));
     }
     const uint32_t nfilt = (n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP;
-    const uint32_t tc_ns = (n <= RT_TC_MAX_SPHERES) ? (n + 127u) / 128u * 128u : 0u;
+    const uint32_t tc_tile = RT_TC_CHUNK * RT_TC_NBUF;   // whole tiles, a multiple of NBUF of them
+    const uint32_t tc_ns = (n <= RT_TC_MAX_SPHERES) ? (n + tc_tile - 1u) / tc_tile * tc_tile : 0u;
     if (tc_ns != c->tc_ns || (tc_ns && !c->d_tcb)) {
         CK(cudaStreamSynchronize(c->stream));
         cudaFree(c->d_tcb); c->d_tcb = nullptr; c->tc_ns = 0;
@@ -553,7 +554,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
             c->counter_slot = 0;
         }
         a.work_counter = c->d_counter + c->counter_slot++;
-        const unsigned long long per_cta = tensor ? 384ull : (unsigned long long)RT_THREADS * RT_RPT;
+        const unsigned long long per_cta = tensor ? (unsigned long long)(RT_TC_WGS * 128) : (unsigned long long)RT_THREADS * RT_RPT;
         unsigned long long want_ctas = (a.total_items + per_cta - 1) / per_cta;
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;

@@ -9,10 +9,10 @@ size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh
     if (exact) return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
     return 128 + ((size_t)npad + nfilt) * 16u + (size_t)RT_FCHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
 }
-// tensor-filter kernel: barriers + B matrix (8 x 16 B per column) + sphere records + 32-sphere mask words (384 ray threads)
+// tensor-filter kernel: barriers + B matrix (8 x 16 B per column) + sphere records + 32-sphere mask words (one per ray thread)
 size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns)
 {
-    return 128 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * 384u * 4u;
+    return 512 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * (RT_TC_WGS * 128u) * 4u;
 }
 size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh)
 {

@@ -13,6 +13,9 @@
 //   reflect/refract/normalize/mix                     src/math.hxx:219-227,294-335
 #pragma once
 #include <cfloat>
+#ifdef RT_TC_PROF
+#include <cstdio>
+#endif
 #include "rt_types.h"
 
 #ifndef RT_EXACT

@@ -18,19 +18,29 @@
 // by the reference test (sphere_candidate_fast) on the few candidates, in increasing sphere index.
 //
 // Per SM: ONE CTA = 3 ray warpgroups (128 rays each, one ray per thread = one TMEM lane) + 3 MMA-issuer warps.
-// TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + 128 columns of accumulators (D).
-// Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full (tcgen05.commit) -> ray warps;
-// empty (accumulators copied to registers) -> issuer.  A chunk is 128 spheres = 4 MMAs (M128 N128 K8).
+// TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + 2 x 64 columns of accumulators (D, double buffered).
+// Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full[b] (tcgen05.commit) -> ray warps;
+// empty[b] (accumulators copied to registers) -> issuer.  A tile is 64 spheres = 4 MMAs (M128 N64 K8); the MMAs of
+// tile c+1 run while the ray warps reduce tile c to sign masks.
 // Epilogue: tcgen05.ld 32 columns -> 32 registers -> sign mask with 16 I2IP (two saturating s32->u8 packs per
 // op) + 8 LOP3 -> the non-empty mask words go to shared memory -> pass 2 as in the FMA-pipe build.
 #pragma once
 
-#define RT_TC_WGS 3                       // ray warpgroups per CTA
+// RT_TC_WGS / RT_TC_CHUNK / RT_TC_NBUF (rt_types.h): ray warpgroups per CTA, spheres per accumulator tile, tiles per warpgroup
 #define RT_TC_RAY_THREADS (RT_TC_WGS * 128)
 #define RT_TC_THREADS (RT_TC_RAY_THREADS + RT_TC_WGS * 32)
-#define RT_TC_CHUNK 128                   // spheres per accumulator tile
 #define RT_TC_KQ 8                        // K = 32 tf32 slots = 8 chunks of 16 bytes
-#define RT_TC_WGCOLS (32 + RT_TC_CHUNK)   // TMEM columns per warpgroup
+#define RT_TC_WGCOLS (32 + RT_TC_NBUF * RT_TC_CHUNK)   // TMEM columns per warpgroup
+#define RT_TC_WGBARS (1 + 2 * RT_TC_NBUF)              // a_ready, full[NBUF], empty[NBUF]
+static_assert(RT_TC_WGS * RT_TC_WGCOLS <= 512, "TMEM has 512 columns");
+static_assert(RT_TC_CHUNK % 32 == 0 && RT_TC_CHUNK >= 32 && RT_TC_CHUNK <= 256, "tile width: whole mask words, one MMA N");
+static_assert((1 + RT_TC_WGS * RT_TC_WGBARS) * 8 <= 448 && 452 + 4 * RT_TC_WGS <= 512, "barriers, TMEM base and done flags live in the first 512 bytes of shared memory");
+
+#ifdef RT_TC_PROF
+#define TC_T(k) do { long long t_ = clock64(); prof[k] += t_ - tprev; tprev = t_; } while (0)
+#else
+#define TC_T(k) do { } while (0)
+#endif
 
 namespace tc {
 
@@ -66,6 +76,14 @@ __device__ __forceinline__ void bar_wait(uint64_t *bar, uint32_t parity)
         "{\n.reg .pred P1;\nTC_WAIT:\n"
         "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
         "@P1 bra TC_DONE;\nbra TC_WAIT;\nTC_DONE:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// issuer-side wait: may sleep long (suspend-time hint), so the idle issuer warps do not take issue slots
+__device__ __forceinline__ void bar_wait_sleep(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n.reg .pred P1;\nTC_WAITS:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, 0x989680;\n"
+        "@P1 bra TC_DONES;\nbra TC_WAITS;\nTC_DONES:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -150,16 +168,16 @@ __device__ __forceinline__ void ray_row(const RtDeviceScene &sc, bool live, floa
 
 }  // namespace tc
 
-// shared memory: [0,128) barriers + TMEM base + done flags | B matrix | sphere records | candidate mask words
-//   bars[0] staging; per warpgroup w: bars[1+3w] a_ready (4 arrivals), [2+3w] full (1), [3+3w] empty (4)
+// shared memory: [0,512) barriers + TMEM base + done flags | B matrix | sphere records | candidate mask words
+//   bars[0] staging; per warpgroup w, at bars + 1 + w * RT_TC_WGBARS: a_ready (4 arrivals), full[NBUF] (1), empty[NBUF] (4)
 __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem_raw + 96);
-    volatile uint32_t *s_done = reinterpret_cast<volatile uint32_t *>(smem_raw + 100);
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem_raw + 448);
+    volatile uint32_t *s_done = reinterpret_cast<volatile uint32_t *>(smem_raw + 452);
     const uint32_t ns = A.sc.tc_ns, npad = A.sc.npad, n = A.sc.n;
-    float4 *s_b = reinterpret_cast<float4 *>(smem_raw + 128);
+    float4 *s_b = reinterpret_cast<float4 *>(smem_raw + 512);
     float4 *s_sph = s_b + (size_t)ns * RT_TC_KQ;
     uint32_t *s_mask = reinterpret_cast<uint32_t *>(s_sph + npad);
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
@@ -167,7 +185,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 
     if (tid == 0) {
         for (int w = 0; w < RT_TC_WGS; ++w) {
-            tc::bar_init(bars + 1 + 3 * w, 4); tc::bar_init(bars + 2 + 3 * w, 1); tc::bar_init(bars + 3 + 3 * w, 4);
+            uint64_t *bw = bars + 1 + w * RT_TC_WGBARS;
+            tc::bar_init(bw, 4);
+            for (int b = 0; b < RT_TC_NBUF; ++b) { tc::bar_init(bw + 1 + b, 1); tc::bar_init(bw + 1 + RT_TC_NBUF + b, 4); }
             s_done[w] = 0u;
         }
     }
@@ -187,22 +207,24 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(RT_TC_CHUNK >> 3) << 17) | ((128u >> 4) << 24);
             const uint64_t bdesc0 = tc::smem_desc(smem_u32(s_b), ns * 16u, 128u);
-            uint64_t *bar = bars + 1 + 3 * w;
+            uint64_t *bar = bars + 1 + w * RT_TC_WGBARS;
             const uint32_t tmem_a = tmem_base + w * RT_TC_WGCOLS, tmem_d = tmem_a + 32;
-            uint32_t uses = 0;
+            uint32_t uses = 0;                                                      // tiles issued so far (tile c uses buffer c & 1)
             for (uint32_t pass = 0;; ++pass) {
-                tc::bar_wait(bar + 0, pass & 1u);                                   // ray rows are in TMEM
+                tc::bar_wait_sleep(bar + 0, pass & 1u);                             // ray rows are in TMEM
                 if (s_done[w]) break;
                 for (uint32_t c = 0; c < nch; ++c) {
-                    if (uses >= 1u) tc::bar_wait(bar + 2, (uses - 1u) & 1u);         // accumulators consumed
+                    const uint32_t b = c % RT_TC_NBUF;                              // nch is a multiple of NBUF: b = uses % NBUF too
+                    if (uses >= RT_TC_NBUF)                                         // previous tile in this buffer consumed
+                        tc::bar_wait_sleep(bar + 1 + RT_TC_NBUF + b, (uses / RT_TC_NBUF - 1u) & 1u);
                     tc::fence_after();
 #pragma unroll
                     for (uint32_t ks = 0; ks < RT_TC_KQ / 2; ++ks) {
                         // K step = 2 k-chunks (2 * ns * 16 bytes apart in s_b); chunk c starts at row 128 c
                         uint64_t bd = bdesc0 + (uint64_t)(((ks * 2u * ns + c * RT_TC_CHUNK) * 16u) >> 4);
-                        tc::mma_tf32_ts(tmem_d, tmem_a + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
+                        tc::mma_tf32_ts(tmem_d + b * RT_TC_CHUNK, tmem_a + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
                     }
-                    tc::mma_commit(bar + 1);
+                    tc::mma_commit(bar + 1 + b);
                     ++uses;
                 }
             }
@@ -213,8 +235,8 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         const uint32_t wg = warp >> 2;
         const uint32_t lane_off = ((warp & 3u) * 32u) << 16;
         const uint32_t tmem_a = tmem_base + wg * RT_TC_WGCOLS + lane_off, tmem_d = tmem_a + 32;
-        uint64_t *bar = bars + 1 + 3 * wg;
-        uint32_t full_parity = 0;
+        uint64_t *bar = bars + 1 + wg * RT_TC_WGBARS;
+        uint32_t full_parity = 0;                   // bit b: parity of the next completion of full[b]
 
         PathSlot S;
         S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
@@ -224,8 +246,13 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
         float best_t = FLT_MAX; int best_i = -1;
 
+#ifdef RT_TC_PROF
+        long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+        uint32_t npass = 0;
+#endif
         for (;;) {
             shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts);
+            TC_T(0);
             const bool live = (S.st == ST_ACTIVE);
             if (!tc::wg_any(1u + wg, S.st != ST_EMPTY)) {                           // whole warpgroup out of work
                 if ((tid & 127u) == 0u) s_done[wg] = 1u;
@@ -233,6 +260,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 if (lane == 0) tc::bar_arrive(bar + 0);
                 break;
             }
+            TC_T(1);
             {
                 float row[32];
                 tc::ray_row(A.sc, live, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, row);
@@ -242,26 +270,35 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 __syncwarp();
                 if (lane == 0) tc::bar_arrive(bar + 0);
             }
+            TC_T(2);
             uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
             for (uint32_t c = 0; c < nch; ++c) {
-                tc::bar_wait(bar + 1, full_parity);
-                full_parity ^= 1u;
+                const uint32_t b = c % RT_TC_NBUF;
+                tc::bar_wait(bar + 1 + b, (full_parity >> b) & 1u);
+                full_parity ^= 1u << b;
                 tc::fence_after();
+                TC_T(3);
 #pragma unroll
-                for (uint32_t h = 0; h < 2; ++h) {
+                for (uint32_t i = 0; i < RT_TC_CHUNK / 32; i += 2) {           // 64 columns (one odd 32 at the end) at a time
+                    const bool two = i + 1 < RT_TC_CHUNK / 32, last = i + 2 >= RT_TC_CHUNK / 32;
                     uint32_t v0[32], v1[32];
-                    RT_TC_LD32(v0, tmem_d + h * 64u);
-                    RT_TC_LD32(v1, tmem_d + h * 64u + 32u);
+                    RT_TC_LD32(v0, tmem_d + b * RT_TC_CHUNK + i * 32u);
+                    if (two) RT_TC_LD32(v1, tmem_d + b * RT_TC_CHUNK + i * 32u + 32u);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    if (h == 1u) {                   // all 128 columns are in registers: hand the tile back
+                    TC_T(4);
+                    if (last) {                      // the whole tile is in registers: hand the buffer back
                         tc::fence_before();
                         __syncwarp();
-                        if (lane == 0) tc::bar_arrive(bar + 2);
+                        if (lane == 0) tc::bar_arrive(bar + 1 + RT_TC_NBUF + b);
                     }
-                    const uint32_t m0 = tc::sign_mask(v0), m1 = tc::sign_mask(v1);
-                    const uint32_t w0 = c * 4u + h * 2u;
+                    const uint32_t w0 = c * (RT_TC_CHUNK / 32) + i;
+                    const uint32_t m0 = tc::sign_mask(v0);
                     if (m0) { s_mask[w0 * RT_TC_RAY_THREADS + tid] = m0; nz |= 0x80000000u >> w0; }
-                    if (m1) { s_mask[(w0 + 1u) * RT_TC_RAY_THREADS + tid] = m1; nz |= 0x80000000u >> (w0 + 1u); }
+                    if (two) {
+                        const uint32_t m1 = tc::sign_mask(v1);
+                        if (m1) { s_mask[(w0 + 1u) * RT_TC_RAY_THREADS + tid] = m1; nz |= 0x80000000u >> (w0 + 1u); }
+                    }
+                    TC_T(5);
                 }
             }
             // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
@@ -289,8 +326,18 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                     if (ci != best_i || ct != best_t) atomicAdd(A.stats + 7, 1ull);
                 }
             }
+            TC_T(6);
+#ifdef RT_TC_PROF
+            ++npass;
+#endif
         }
 
+#ifdef RT_TC_PROF
+        if (blockIdx.x == 3 && lane == 0)
+            printf("warp %2u passes %u | per pass: shade %6.0f  wg-barrier %5.0f  row+st %5.0f  wait-mma %6.0f  ldtm %5.0f  masks %6.0f  pass2 %6.0f\n", warp, npass,
+                   (double)prof[0] / npass, (double)prof[1] / npass, (double)prof[2] / npass, (double)prof[3] / npass, (double)prof[4] / npass,
+                   (double)prof[5] / npass, (double)prof[6] / npass);
+#endif
         uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
 #pragma unroll
         for (int k = 0; k < 5; ++k) {

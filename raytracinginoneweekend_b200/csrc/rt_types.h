@@ -100,6 +100,16 @@ cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 namespace rtf {
 cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
 }
+// tensor-filter kernel shape (rt_tensor.cuh): RT_TC_WGS ray warpgroups x (32 + RT_TC_NBUF * RT_TC_CHUNK) TMEM columns <= 512
+#ifndef RT_TC_WGS
+#define RT_TC_WGS 3
+#endif
+#ifndef RT_TC_CHUNK
+#define RT_TC_CHUNK 128
+#endif
+#ifndef RT_TC_NBUF
+#define RT_TC_NBUF 1
+#endif
 #define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
 #define RT_TC_MIN_SPHERES 48u
 #define RT_TC_MAX_SPHERES 1024u   // tensor-filter path: B matrix (128 B per sphere) + records + masks fit in shared memory
