@@ -17,7 +17,8 @@
 // tools/proto_tc.cu), so no sphere the reference test accepts is dropped; the hit that is returned is decided
 // by the reference test (sphere_candidate_fast) on the few candidates, in increasing sphere index.
 //
-// Per SM: ONE CTA = 3 ray warpgroups (128 rays each, one ray per thread = one TMEM lane) + 3 MMA-issuer warps.
+// Per SM: ONE CTA = RT_TC_WGS ray warpgroups (128 rays each, one ray per thread = one TMEM lane) + one warpgroup of
+// MMA-issuer warps (one per ray warpgroup; with 4 ray warpgroups they give their registers away: setmaxnreg).
 // TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + 2 x 64 columns of accumulators (D, double buffered).
 // Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full[b] (tcgen05.commit) -> ray warps;
 // empty[b] (accumulators copied to registers) -> issuer.  A tile is 64 spheres = 4 MMAs (M128 N64 K8); the MMAs of
@@ -28,7 +29,9 @@
 
 // RT_TC_WGS / RT_TC_CHUNK / RT_TC_NBUF (rt_types.h): ray warpgroups per CTA, spheres per accumulator tile, tiles per warpgroup
 #define RT_TC_RAY_THREADS (RT_TC_WGS * 128)
-#define RT_TC_THREADS (RT_TC_RAY_THREADS + RT_TC_WGS * 32)
+#define RT_TC_THREADS (RT_TC_RAY_THREADS + 128)          // + one warpgroup of MMA issuers (one warp per ray warpgroup)
+// with 4 ray warpgroups: 640 threads x 96 registers at launch; the issuer warpgroup drops to 24, the ray warpgroups take 112
+// (the pool is the CTA's own allocation: 128 x 72 freed >= 4 x 128 x 16 taken)
 #define RT_TC_KQ 8                        // K = 32 tf32 slots = 8 chunks of 16 bytes
 #define RT_TC_WGCOLS (32 + RT_TC_NBUF * RT_TC_CHUNK)   // TMEM columns per warpgroup
 #define RT_TC_WGBARS (1 + 2 * RT_TC_NBUF)              // a_ready, full[NBUF], empty[NBUF]
@@ -51,16 +54,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
     return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
            ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
 }
-// D[tmem] (+)= A[tmem] * B[smem]^T, M = 128, N = RT_TC_CHUNK, K = 8 (tf32), issued by ONE thread
+// D[tmem] (+)= A[tmem] * B[smem]^T, M = 128, N = RT_TC_CHUNK, K = 8 (tf32).  Called by a CONVERGED warp with
+// warp-uniform operands; one elected lane issues (keeps the operands in uniform registers: no per-issue election loop)
 __device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
 {
-    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}"
+    asm volatile("{\n.reg .pred p, pe;\nsetp.ne.b32 p, %4, 0;\nelect.sync _|pe, 0xffffffff;\n"
+                 "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}"
                  ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void mma_commit(uint64_t *bar)
 {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
+                 "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void bar_init(uint64_t *bar, uint32_t count)
 {
@@ -124,6 +129,9 @@ __device__ __forceinline__ float tf32_round(float x)
 
 // Sign mask of 32 accumulator words: bit (8p + j) <=> word 4j + 3 - p is a positive float.  The host places
 // sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2), so that __clz order = sphere order.
+// 16 I2IP (two saturating s32->u8 packs per op) + 8 LOP3.  Measured alternatives (same kernel, huge scene):
+// FP32 Horner chains of sat(-2^100 v) on the FMA pipe, funnel shifts on the ALU pipe, or both on alternating
+// words: 6-10 % slower (more live registers, 64 instead of 24 issue slots per word).
 __device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
 {
     uint32_t m = 0;
@@ -204,34 +212,40 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     if (warp >= RT_TC_WGS * 4) {
         // ============================================================ MMA issuer: one thread per warpgroup
         const uint32_t w = warp - RT_TC_WGS * 4;
-        if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(RT_TC_CHUNK >> 3) << 17) | ((128u >> 4) << 24);
-            const uint64_t bdesc0 = tc::smem_desc(smem_u32(s_b), ns * 16u, 128u);
-            uint64_t *bar = bars + 1 + w * RT_TC_WGBARS;
-            const uint32_t tmem_a = tmem_base + w * RT_TC_WGCOLS, tmem_d = tmem_a + 32;
-            uint32_t uses = 0;                                                      // tiles issued so far (tile c uses buffer c & 1)
-            for (uint32_t pass = 0;; ++pass) {
-                tc::bar_wait_sleep(bar + 0, pass & 1u);                             // ray rows are in TMEM
-                if (s_done[w]) break;
-                for (uint32_t c = 0; c < nch; ++c) {
-                    const uint32_t b = c % RT_TC_NBUF;                              // nch is a multiple of NBUF: b = uses % NBUF too
-                    if (uses >= RT_TC_NBUF)                                         // previous tile in this buffer consumed
-                        tc::bar_wait_sleep(bar + 1 + RT_TC_NBUF + b, (uses / RT_TC_NBUF - 1u) & 1u);
-                    tc::fence_after();
+#if RT_TC_WGS >= 4
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");                        // hand registers to the ray warpgroups
+#endif
+        if (w < RT_TC_WGS) {
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(RT_TC_CHUNK >> 3) << 17) | ((128u >> 4) << 24);
+        const uint64_t bdesc0 = tc::smem_desc(smem_u32(s_b), ns * 16u, 128u);
+        uint64_t *bar = bars + 1 + w * RT_TC_WGBARS;
+        const uint32_t tmem_a = tmem_base + w * RT_TC_WGCOLS, tmem_d = tmem_a + 32;
+        uint32_t uses = 0;                                                          // tiles issued so far
+        for (uint32_t pass = 0;; ++pass) {
+            tc::bar_wait_sleep(bar + 0, pass & 1u);                                 // ray rows are in TMEM
+            if (s_done[w]) break;
+            for (uint32_t c = 0; c < nch; ++c) {
+                const uint32_t b = c % RT_TC_NBUF;                                  // nch is a multiple of NBUF: b = uses % NBUF too
+                if (uses >= RT_TC_NBUF)                                             // previous tile in this buffer consumed
+                    tc::bar_wait_sleep(bar + 1 + RT_TC_NBUF + b, (uses / RT_TC_NBUF - 1u) & 1u);
+                tc::fence_after();
 #pragma unroll
-                    for (uint32_t ks = 0; ks < RT_TC_KQ / 2; ++ks) {
-                        // K step = 2 k-chunks (2 * ns * 16 bytes apart in s_b); chunk c starts at row 128 c
-                        uint64_t bd = bdesc0 + (uint64_t)(((ks * 2u * ns + c * RT_TC_CHUNK) * 16u) >> 4);
-                        tc::mma_tf32_ts(tmem_d + b * RT_TC_CHUNK, tmem_a + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
-                    }
-                    tc::mma_commit(bar + 1 + b);
-                    ++uses;
+                for (uint32_t ks = 0; ks < RT_TC_KQ / 2; ++ks) {
+                    // K step = 2 k-chunks (2 * ns * 16 bytes apart in s_b); tile c starts at row RT_TC_CHUNK * c
+                    uint64_t bd = bdesc0 + (uint64_t)(((ks * 2u * ns + c * RT_TC_CHUNK) * 16u) >> 4);
+                    tc::mma_tf32_ts(tmem_d + b * RT_TC_CHUNK, tmem_a + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
                 }
+                tc::mma_commit(bar + 1 + b);
+                ++uses;
             }
+        }
         }
         __syncwarp();
     } else {
         // ============================================================ ray warps: one path per thread
+#if RT_TC_WGS >= 4
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+#endif
         const uint32_t wg = warp >> 2;
         const uint32_t lane_off = ((warp & 3u) * 32u) << 16;
         const uint32_t tmem_a = tmem_base + wg * RT_TC_WGCOLS + lane_off, tmem_d = tmem_a + 32;

@@ -102,10 +102,10 @@ cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaS
 }
 // tensor-filter kernel shape (rt_tensor.cuh): RT_TC_WGS ray warpgroups x (32 + RT_TC_NBUF * RT_TC_CHUNK) TMEM columns <= 512
 #ifndef RT_TC_WGS
-#define RT_TC_WGS 3
+#define RT_TC_WGS 4
 #endif
 #ifndef RT_TC_CHUNK
-#define RT_TC_CHUNK 128
+#define RT_TC_CHUNK 96
 #endif
 #ifndef RT_TC_NBUF
 #define RT_TC_NBUF 1

@@ -13,7 +13,8 @@ import pytest
 
 from conftest import assert_bits_equal
 from raytracinginoneweekend_b200 import scenes
-from raytracinginoneweekend_b200.backend import FLAG_BRUTE, FLAG_EXACT, FLAG_LBVH, RtError
+from raytracinginoneweekend_b200.backend import (FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH,
+                                                 RtError)
 
 pytestmark = pytest.mark.gpu
 
@@ -211,6 +212,54 @@ def test_fast_and_exact_builds_agree_statistically(be):
     # same seeds and counters: almost every path is identical, a few diverge at grazing hits
     assert np.sqrt(((a - b) ** 2).mean()) < 0.01
     assert abs(a.mean() - b.mean()) < 1e-3
+
+
+# ------------------------------------------------------------------ tensor-core candidate filter (throughput build)
+def random_scene(n, seed, W, H):
+    """n spheres of mixed sizes and materials around the camera's view, plus a huge ground sphere when n > 3."""
+    rng = np.random.default_rng(seed)
+    sc = scenes.huge_scene(W, H)
+    sph = np.zeros((n, 4), dtype=np.float32)
+    sph[:, 0] = rng.uniform(-12, 12, n); sph[:, 1] = rng.uniform(-4, 3, n); sph[:, 2] = rng.uniform(-14, 6, n)
+    sph[:, 3] = rng.choice([0.2, 0.2, 0.2, 0.7, 1.5], n) * rng.choice([1.0, 1.0, 1.0, -0.95], n)
+    if n > 3:
+        sph[0] = (3.0, -1003.2, -4.0, 1000.0)
+    mat = rng.integers(0, sc.m, n).astype(np.uint32)
+    return scenes.Scene(f"random{n}", sph, mat, sc.materials, sc.mat_kind, sc.camera)
+
+
+@pytest.mark.parametrize("n", [48, 95, 96, 97, 192, 193, 488, 777, 1024])
+def test_tensor_filter_never_drops_a_hit(be, n):
+    """RT_FLAG_FILTER_CHECK re-runs the candidate test over ALL spheres for every segment and counts the
+    segments whose closest hit differs from the filtered one: the tcgen05 filter is a superset filter, so 0.
+    Sphere counts straddle the 96-column accumulator tiles and the 1024-sphere limit of the tensor path."""
+    W, H = 192, 108
+    sc = scenes.huge_scene(W, H) if n == 488 else random_scene(n, 1000 + n, W, H)
+    setup(be, sc, W, H)
+    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK)
+    st = be.stats()
+    assert st["segments"] > 2 * W * H
+    assert st["filter_misses"] == 0, f"{st['filter_misses']} of {st['segments']} segments lost their closest hit"
+    be.clear(); be.reset_stats()
+    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK | FLAG_FILTER_FMA)
+    st = be.stats()
+    assert st["filter_misses"] == 0, "FMA-pipe filter dropped a hit"
+
+
+def test_tensor_and_fma_filters_render_the_same_image(be):
+    """Both throughput kernels trace the same counter-based paths; they differ only by how the compiler contracts
+    the shading arithmetic, so a few paths diverge at grazing hits and every pixel agrees to Monte Carlo precision."""
+    W, H = 160, 90
+    setup(be, scenes.huge_scene(W, H), W, H)
+    be.render(512, 50, seed=3, flags=0)
+    a = be.readback_f32().astype(np.float64); sa = be.stats()
+    be.clear(); be.reset_stats()
+    be.render(512, 50, seed=3, flags=FLAG_FILTER_FMA)
+    b = be.readback_f32().astype(np.float64); sb = be.stats()
+    assert np.sqrt(((a - b) ** 2).mean()) < 0.01
+    assert abs(a.mean() - b.mean()) < 1e-3
+    assert abs(sa["segments"] - sb["segments"]) < 2e-3 * sb["segments"]
+    assert sa["samples"] == sb["samples"] == W * H * 512
 
 
 # ------------------------------------------------------------------ resolve + e2e call
