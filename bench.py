@@ -251,6 +251,8 @@ def run_gpu_arm(args):
     torch.cuda.synchronize()
 
     probe = be.fp32_peak_probe()
+    finfo = be.filter_info()
+    tprobe = be.tf32_peak_probe() if finfo["tensor"] else None
     be.reset_stats()
     clocks = ClockSampler(local)
     if rank == 0:
@@ -316,23 +318,47 @@ def run_gpu_arm(args):
         total = float(W) * H * spp * args.steps
         value = total / (dev_ms * 1e-3) / 1e9
         e2e_value = float(W) * H * spp * e2e_steps / (e2e_ms * 1e-3) / 1e9
-        # roofline of the dominant kernel (k_render, one launch per step at N=1): algorithmic FLOP / launch time
+        # roofline of the dominant kernel (one launch per step at N=1), live: device counters / CUDA-event launch time.
+        #  * brute force <= 1024 spheres: k_render_tc.  The sphere tests run on the tensor pipe as a TF32x3 product
+        #    (64 flop per ray x padded sphere column: K = 32 slots), so the bound is "tensor": executed tensor FLOP/s
+        #    against the TF32 peak measured in this run.  The SURVEY 8(d) algorithmic FP32 count is reported next to it.
+        #  * otherwise k_render on the FP32 FMA pipe: SURVEY 8(d) algorithmic FLOP/s against the measured FMA peak.
         render_ms_per_launch = st["render_ms"] / max(1, args.steps)
         flop = algorithmic_flop(st["segments"], st["samples"], W * H * args.steps, sc.n) / max(1, args.steps)
         achieved = flop / (render_ms_per_launch * 1e-3) / 1e12
         traffic = None
         prof = os.path.join(ROOT, "profiles", "ncu_summary.json")
+        kname = "k_render_tc" if finfo["tensor"] else "k_render"
         if os.path.exists(prof):
             try:
-                traffic = json.load(open(prof)).get("k_render", {}).get("dram_bytes_per_launch")
+                traffic = json.load(open(prof)).get(kname, {}).get("dram_bytes_per_launch")
             except Exception:
                 traffic = None
+        fp32_model = {"achieved": achieved, "peak": probe["tflops"], "unit": "TFLOP/s", "frac": achieved / probe["tflops"],
+                      "flop_model": "SURVEY 8(d): segments*(18*N+64) + samples*32 + pixels*8, segments/samples from device counters",
+                      "peak_source": "FMA-chain probe measured in this run (rt_fp32_peak_probe); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.45"}
+        if finfo["tensor"]:
+            tflop = st["segments"] * finfo["columns"] * 2.0 * finfo["k"] / max(1, args.steps)
+            tach = tflop / (render_ms_per_launch * 1e-3) / 1e12
+            roofline = {"bound": "tensor", "achieved": tach, "peak": tprobe["tflops"], "unit": "TFLOP/s",
+                        "frac": tach / tprobe["tflops"], "traffic": traffic,
+                        "kernel": "k_render_tc (persistent bounce loop; candidate filter = TF32x3 tcgen05 product, accumulators in TMEM)",
+                        "peak_source": "tcgen05.mma kind::tf32 stream measured in this run (rt_tf32_peak_probe); nominal dense TF32 1.1 PFLOP/s",
+                        "flop_model": f"segments * {finfo['columns']} sphere columns * K={finfo['k']} * 2 (split-TF32 product of the ray x sphere discriminant form)",
+                        "note": "the kernel is bound by issue slots of the sign-mask epilogue and the shading code, not by the tensor pipe; "
+                                "fp32_algorithmic is SURVEY 8(d)'s FP32 model (a fraction above 1 = more sphere tests per second than the FMA pipe could execute)",
+                        "fp32_algorithmic": fp32_model, "ms_per_launch": render_ms_per_launch, "rank": 0}
+            accel = "brute force: tensor-core candidate filter (sphere matrix in shared memory via TMA, accumulators in TMEM) + reference test on candidates"
+        else:
+            roofline = dict(fp32_model, bound="fp32", traffic=traffic, kernel="k_render (persistent bounce loop: sphere tests + shading)",
+                            ms_per_launch=render_ms_per_launch, rank=0)
+            accel = "brute-force (shared-memory SoA spheres)"
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": wname, "scene": scene_name, "n_spheres": sc.n, "width": W, "height": H, "spp": spp,
-                       "max_depth": DEPTH, "seed": SEED, "accel": "brute-force (shared-memory SoA spheres)",
+                       "max_depth": DEPTH, "seed": SEED, "accel": accel,
                        "parallelism": f"tile-sharded x{world}, stealing, NCCL reduce to rank 0" if world > 1 else "1 GPU",
                        "l2": "flushed between timed steps (256 MiB write)",
                        "segments_per_sample": segments / max(1.0, samples)},
@@ -342,12 +368,7 @@ def run_gpu_arm(args):
                     "call": "rt_render_frame (cuda_impl-shaped: host scene in, host RGB8 out)" if world == 1
                             else "rt_scene_upload + tile-stolen rt_render_tiles + NCCL reduce + D2H on rank 0"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": probe["tflops"], "unit": "TFLOP/s",
-                         "frac": achieved / probe["tflops"], "traffic": traffic,
-                         "kernel": "k_render (persistent bounce loop: sphere tests + shading)",
-                         "peak_source": "FMA-chain probe measured in this run (rt_fp32_peak_probe); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.45",
-                         "flop_model": "segments*(18*N+64) + samples*32 + pixels*8, segments/samples from device counters",
-                         "ms_per_launch": render_ms_per_launch, "rank": 0},
+            "roofline": roofline,
             "wall_s": wall_s,
         }
         if world == 1 and not args.no_cpu_baseline:

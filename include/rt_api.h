@@ -179,6 +179,12 @@ RT_EXPORT int rt_write_ppm(const char *path, uint32_t width, uint32_t height, co
 /* FP32 FMA-chain microbenchmark: the measured denominator of the FP32 roofline.
  * out = {TFLOP/s achieved (FMA = 2 flop), kernel ms, SM count}. */
 RT_EXPORT int rt_fp32_peak_probe(rt_ctx *ctx, double out3[3]);
+/* TF32 tensor-core peak of this device measured with a tcgen05.mma stream (M128 N256 K8, one CTA per SM):
+ * out = {TFLOP/s, best ms, SM count}.  Denominator of the tensor roofline of the candidate filter (bench.py). */
+RT_EXPORT int rt_tf32_peak_probe(rt_ctx *ctx, double out[3]);
+/* Candidate filter the throughput build runs for the uploaded scene: out = {1 tensor cores | 0 FMA pipe,
+ * padded sphere columns per ray, K of the filter product (tf32 slots), rays resident per CTA}. */
+RT_EXPORT int rt_filter_info(rt_ctx *ctx, uint32_t out[4]);
 
 /* ---- node-level tile queue (multi-GPU dynamic tile stealing, one process per GPU) -------------
  * RT_QUEUE_SLOTS lock-free counters (one cache line each) in POSIX shared memory, shared by the ranks of

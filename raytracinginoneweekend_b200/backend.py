@@ -26,7 +26,7 @@ EXPORTS = [
     "rt_render_tiles",
     "rt_primary_hits", "rt_closest_hits", "rt_readback_rgb8", "rt_readback_f32", "rt_readback_accum",
     "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
-    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe",
+    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info",
     "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
 ]
 
@@ -107,6 +107,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_stats_reset.argtypes = [vp]
     lib.rt_write_ppm.argtypes = [C.c_char_p, u32, u32, vp]
     lib.rt_fp32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
+    lib.rt_tf32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
+    lib.rt_filter_info.argtypes = [vp, C.POINTER(C.c_uint32)]
     lib.rt_queue_open.argtypes = [C.POINTER(vp), C.c_char_p, i32]
     lib.rt_queue_reset.argtypes = [vp, u32, u64]
     lib.rt_queue_next.argtypes = [vp, u32, u64, C.POINTER(u64)]
@@ -271,6 +273,16 @@ class Backend:
 
     def reset_stats(self):
         _check(self.lib, self.lib.rt_stats_reset(self.ctx))
+
+    def tf32_peak_probe(self):
+        out = (C.c_double * 3)()
+        _check(self.lib, self.lib.rt_tf32_peak_probe(self.ctx, out))
+        return dict(tflops=out[0], ms=out[1], sm_count=int(out[2]))
+
+    def filter_info(self):
+        out = (C.c_uint32 * 4)()
+        _check(self.lib, self.lib.rt_filter_info(self.ctx, out))
+        return dict(tensor=bool(out[0]), columns=int(out[1]), k=int(out[2]), rays_per_cta=int(out[3]))
 
     def fp32_peak_probe(self):
         out = (C.c_double * 3)()

@@ -360,7 +360,7 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         // centres (keeps |c - g| small for the many small spheres whatever the ground sphere does).
         // Slots: 9 terms {xx,yy,zz,xy,xz,yz,x,y,z} x (f_h, f_l, f_h) | w_h, w_m, w_l | 1, 1 with
         // w = r^2 - |c|^2 + eps (|c|^2 + r^2); hi parts are TF32 (10-bit mantissa, round to nearest), evaluated in double.
-        // Column pos = 32 b + v holds sphere 32 b + 7 + 8 (v & 3) - (v >> 2): the sign-mask bit order (tc::sign_mask).
+        // RT_TC_MASKMODE 0: column pos = 32 b + v holds sphere 32 b + 7 + 8 (v & 3) - (v >> 2), the I2IP sign-mask bit order.
         float *hb = (float *)(h + b_sph + b_rad + b_meta + b_mat + b_filt);
         std::memset(hb, 0, b_tcb);
         std::vector<float> med(n);
@@ -377,7 +377,11 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         };
         auto put = [&](uint32_t pos, uint32_t slot, float v) { hb[((size_t)(slot >> 2) * tc_ns + pos) * 4 + (slot & 3u)] = v; };
         for (uint32_t pos = 0; pos < tc_ns; ++pos) {
+#if RT_TC_MASKMODE == 0
             const uint32_t v = pos & 31u, i = (pos & ~31u) + 7u + 8u * (v & 3u) - (v >> 2);
+#else
+            const uint32_t i = pos;                                     // sign masks in column order
+#endif
             if (i >= n) { put(pos, 27, -3.0e38f); continue; }           // padding: never a candidate
             const rt_sphere &sp = spheres[i];
             const double x = (double)sp.cx - g[0], y = (double)sp.cy - g[1], z = (double)sp.cz - g[2], r2 = (double)sp.r * sp.r;
@@ -805,6 +809,46 @@ int rt_fp32_peak_probe(rt_ctx *c, double out[3])
     out[0] = flop / (best * 1e-3) * 1e-12;
     out[1] = best;
     out[2] = c->sm_count;
+    return RT_OK;
+}
+
+int rt_tf32_peak_probe(rt_ctx *c, double out[3])
+{
+    if (!c || !out) return fail(RT_ERR_INVALID, "rt_tf32_peak_probe: NULL argument");
+    CK(cudaSetDevice(c->device));
+    const int blocks = c->sm_count, iters = 4096;
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    CK(rt_launch_tf32_probe(blocks, 16, c->stream));   // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CK(cudaEventRecord(a, c->stream));
+        CK(rt_launch_tf32_probe(blocks, iters, c->stream));
+        CK(cudaEventRecord(b, c->stream));
+        CK(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        if (ms < best) best = ms;
+    }
+    c->hs.launches += 6;
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    double flop = (double)blocks * iters * 4.0 * (128.0 * 256.0 * 8.0) * 2.0;
+    out[0] = flop / (best * 1e-3) * 1e-12;
+    out[1] = best;
+    out[2] = c->sm_count;
+    return RT_OK;
+}
+
+int rt_filter_info(rt_ctx *c, uint32_t out[4])
+{
+    if (!c || !out) return fail(RT_ERR_INVALID, "rt_filter_info: NULL argument");
+    // which candidate filter the throughput build runs for the uploaded scene, and the GEMM shape per 128 rays
+    const bool tensor = c->d_tcb && c->n >= RT_TC_MIN_SPHERES;
+    out[0] = tensor ? 1u : 0u;
+    out[1] = tensor ? c->tc_ns : c->nfilt;      // sphere columns per ray (padded)
+    out[2] = tensor ? 32u : 0u;                 // K (tf32 slots)
+    out[3] = tensor ? (uint32_t)(RT_TC_WGS * 128) : (uint32_t)(RT_THREADS * RT_RPT);   // rays resident per CTA
     return RT_OK;
 }
 

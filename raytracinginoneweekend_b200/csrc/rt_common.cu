@@ -102,6 +102,58 @@ __global__ void __launch_bounds__(256) k_fp32_probe(float *out, float a, float b
     if (s == 123.456f) out[0] = s;   // keeps the chains alive without a store on the timed path
 }
 
+// TF32 tensor peak probe: one CTA per SM, one thread streams tcgen05.mma kind::tf32 (M128 N256 K8, A from TMEM, B from
+// shared memory) into one accumulator tile; measures the denominator of the tensor roofline in the same run.
+__device__ __forceinline__ uint32_t probe_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__global__ void __launch_bounds__(128, 1) k_tf32_probe(int iters)
+{
+    extern __shared__ __align__(1024) unsigned char psm[];
+    float *s = reinterpret_cast<float *>(psm);                                 // B: 256 rows x K=32 tf32 = 32 KB of zeros
+    uint64_t *bar = reinterpret_cast<uint64_t *>(psm + 32768);
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(psm + 32768 + 8);
+    for (int i = threadIdx.x; i < 8192; i += 128) s[i] = 0.f;
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(probe_smem_u32(bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(probe_smem_u32(s_tmem)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tm = *s_tmem;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((256u >> 3) << 17) | ((128u >> 4) << 24);
+        const uint32_t sa = probe_smem_u32(s);
+        const uint64_t bdesc = (uint64_t)((sa >> 4) & 0x3fffu) | ((uint64_t)((256u * 16u) >> 4) << 16) | ((uint64_t)(128u >> 4) << 32) | (1ull << 46);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (uint32_t ks = 0; ks < 4; ++ks) {
+                uint64_t bd = bdesc + (uint64_t)((ks * 2u * 256u * 16u) >> 4);
+                uint32_t acc = ks > 0 ? 1u : 0u;
+                asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}"
+                             ::"r"(tm + 64u), "r"(tm + ks * 8u), "l"(bd), "r"(idesc), "r"(acc) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(probe_smem_u32(bar)) : "memory");
+        asm volatile("{\n.reg .pred P1;\nPRB_W:\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], 0;\n@P1 bra PRB_D;\nbra PRB_W;\nPRB_D:\n}"
+                     ::"r"(probe_smem_u32(bar)) : "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tm));
+}
+
+cudaError_t rt_launch_tf32_probe(int blocks, int iters, cudaStream_t s)
+{
+    const size_t smem = 32768 + 64;
+    k_tf32_probe<<<blocks, 128, smem, s>>>(iters);
+    return cudaGetLastError();
+}
+
 cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint4 tile0, const uint4 *tiles, uint32_t nt,
                                 uint32_t TP, unsigned long long spp, cudaStream_t s)
 {

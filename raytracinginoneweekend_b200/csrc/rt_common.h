@@ -7,3 +7,5 @@ cudaError_t rt_launch_add_count(unsigned long long *accum, uint32_t W, uint4 til
 cudaError_t rt_launch_resolve(const unsigned long long *accum, unsigned long long npix, unsigned char *rgb8, float *meanf,
                               cudaStream_t s);
 cudaError_t rt_launch_fp32_probe(float *scratch, int blocks, int iters, cudaStream_t s);
+// streams iters x 4 tcgen05.mma kind::tf32 (M128 N256 K8) per CTA: 128*256*8 MACs each
+cudaError_t rt_launch_tf32_probe(int blocks, int iters, cudaStream_t s);

@@ -19,10 +19,11 @@
 //
 // Per SM: ONE CTA = RT_TC_WGS ray warpgroups (128 rays each, one ray per thread = one TMEM lane) + one warpgroup of
 // MMA-issuer warps (one per ray warpgroup; with 4 ray warpgroups they give their registers away: setmaxnreg).
-// TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + 2 x 64 columns of accumulators (D, double buffered).
+// TMEM (512 columns): per warpgroup 32 columns of ray rows (A) + RT_TC_NBUF accumulator tiles (D) of RT_TC_CHUNK columns.
 // Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full[b] (tcgen05.commit) -> ray warps;
-// empty[b] (accumulators copied to registers) -> issuer.  A tile is 64 spheres = 4 MMAs (M128 N64 K8); the MMAs of
-// tile c+1 run while the ray warps reduce tile c to sign masks.
+// empty[b] (accumulators copied to registers) -> issuer.  A tile is 64 spheres = 4 MMAs (M128 N64 K8).
+// Measured shapes (huge scene, Gsamples/s): 3 warpgroups x 128 columns 1.33, 3 x (2 x 64) 1.35, 4 x 96 1.43, 4 x 64 1.46,
+// 4 x (3 x 32) 1.18; candidate tests inlined per tile (RT_TC_INLINE_PASS2) 1.42.
 // Epilogue: tcgen05.ld 32 columns -> 32 registers -> sign mask with 16 I2IP (two saturating s32->u8 packs per
 // op) + 8 LOP3 -> the non-empty mask words go to shared memory -> pass 2 as in the FMA-pipe build.
 #pragma once
@@ -127,12 +128,19 @@ __device__ __forceinline__ float tf32_round(float x)
                    "f"(v[24]), "f"(v[25]), "f"(v[26]), "f"(v[27]), "f"(v[28]), "f"(v[29]), "f"(v[30]), "f"(v[31])         \
                  : "memory")
 
-// Sign mask of 32 accumulator words: bit (8p + j) <=> word 4j + 3 - p is a positive float.  The host places
-// sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2), so that __clz order = sphere order.
-// 16 I2IP (two saturating s32->u8 packs per op) + 8 LOP3.  Measured alternatives (same kernel, huge scene):
-// FP32 Horner chains of sat(-2^100 v) on the FMA pipe, funnel shifts on the ALU pipe, or both on alternating
-// words: 6-10 % slower (more live registers, 64 instead of 24 issue slots per word).
-__device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
+// Sign masks of 32 accumulator words -> one 32-bit candidate mask whose __clz order is the sphere order.
+// RT_TC_MASKMODE (rt_types.h) selects the reduction; the host lays the sphere matrix out accordingly:
+//   0  I2IP: 16 two-value saturating s32->u8 packs + 8 LOP3.  bit (8p + j) <=> word 4j + 3 - p is a positive float;
+//      the host places sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2).  Fewest issue slots (24
+//      per word) but I2IP is a slow-rate instruction (~8 cycles per warp instruction per SM sub-partition).
+//   1-3  the ray rows are stored NEGATED, a candidate is a NEGATIVE accumulator, word i -> bit 31 - i, identity layout:
+//      1  FMA pipe: t = sat(-2^100 v) in {0,1}, FP32 Horner chains c = 2c + t (exact: chains stay below 2^16), the
+//         two 16-bit halves read out of the mantissa with the 2^23 trick + one PRMT;
+//      2  ALU pipe: funnel shifts, 4 chains of 8 + 3 combines;
+//      3  FMA pipe on even words, ALU pipe on odd words (both pipes at once).
+//      (An accumulator of magnitude below 2^-100 would make t fractional; the terms are O(1)..O(|c|^2) with 24-bit
+//       significands, so a nonzero sum that small does not occur -- and a true candidate is >= eps * scale away from 0.)
+__device__ __forceinline__ uint32_t sign_mask_i2ip(const uint32_t (&v)[32])
 {
     uint32_t m = 0;
 #pragma unroll
@@ -143,6 +151,42 @@ __device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
         m |= w & (0x01010101u << j);
     }
     return m;
+}
+__device__ __forceinline__ uint32_t sign_mask_alu(const uint32_t (&v)[32])
+{
+    uint32_t c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        c[k] = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) c[k] = __funnelshift_l(v[8 * k + i], c[k], 1);
+    }
+    return (c[0] << 24) | (c[1] << 16) | (c[2] << 8) | c[3];
+}
+__device__ __forceinline__ uint32_t sign_mask_fma(const uint32_t (&v)[32])
+{
+    float c[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        c[k] = __saturatef(__uint_as_float(v[8 * k]) * -1.2676506002282294e30f);
+#pragma unroll
+        for (int i = 1; i < 8; ++i) c[k] = fmaf(c[k], 2.f, __saturatef(__uint_as_float(v[8 * k + i]) * -1.2676506002282294e30f));
+    }
+    const float hi = fmaf(c[0], 256.f, c[1]) + 8388608.f, lo = fmaf(c[2], 256.f, c[3]) + 8388608.f;
+    return __byte_perm(__float_as_uint(lo), __float_as_uint(hi), 0x5410);
+}
+template <int WORD>
+__device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
+{
+#if RT_TC_MASKMODE == 0
+    return sign_mask_i2ip(v);
+#elif RT_TC_MASKMODE == 1
+    return sign_mask_fma(v);
+#elif RT_TC_MASKMODE == 2
+    return sign_mask_alu(v);
+#else
+    return (WORD & 1) ? sign_mask_alu(v) : sign_mask_fma(v);
+#endif
 }
 
 // Ray -> the 32 A-operand slots (slot order must match tc_sphere_row on the host, rt_api.cu)
@@ -158,18 +202,22 @@ __device__ __forceinline__ void ray_row(const RtDeviceScene &sc, bool live, floa
     float uo = ux * ox + uy * oy + uz * oz;
     float qx = ox - uo * ux, qy = oy - uo * uy, qz = oz - uo * uz;
     float kk = fmaf(sc.tc_eps, oo, -(qx * qx + qy * qy + qz * qz));
+    // RT_TC_NEG = -1: the row holds -q's coefficients, candidates come out as negative accumulators
     float co[9] = {ux * ux, uy * uy, uz * uz, 2.f * ux * uy, 2.f * ux * uz, 2.f * uy * uz, 2.f * qx, 2.f * qy, 2.f * qz};
+#pragma unroll
+    for (int t = 0; t < 9; ++t) co[t] *= RT_TC_NEG;
+    kk *= RT_TC_NEG;
     if (!ok) {                              // no candidates: d = 0 / non-finite ray (the reference test rejects it), idle slot
 #pragma unroll
         for (int t = 0; t < 9; ++t) co[t] = 0.f;
-        kk = -3.0e38f;
+        kk = -3.0e38f * RT_TC_NEG;
     }
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
         float h = tf32_round(co[t]);
         row[3 * t + 0] = h; row[3 * t + 1] = h; row[3 * t + 2] = co[t] - h;
     }
-    row[27] = 1.f; row[28] = 1.f; row[29] = 1.f;
+    row[27] = RT_TC_NEG; row[28] = RT_TC_NEG; row[29] = RT_TC_NEG;
     float h = tf32_round(kk);
     row[30] = h; row[31] = kk - h;
 }
@@ -286,12 +334,16 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
             }
             TC_T(2);
             uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
+            best_t = FLT_MAX; best_i = -1;
+            const float ray_a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+            const float ray_inv_a = __frcp_rn(ray_a);
             for (uint32_t c = 0; c < nch; ++c) {
                 const uint32_t b = c % RT_TC_NBUF;
                 tc::bar_wait(bar + 1 + b, (full_parity >> b) & 1u);
                 full_parity ^= 1u << b;
                 tc::fence_after();
                 TC_T(3);
+#if RT_TC_MASKMODE == 0
 #pragma unroll
                 for (uint32_t i = 0; i < RT_TC_CHUNK / 32; i += 2) {           // 64 columns (one odd 32 at the end) at a time
                     const bool two = i + 1 < RT_TC_CHUNK / 32, last = i + 2 >= RT_TC_CHUNK / 32;
@@ -306,20 +358,51 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                         if (lane == 0) tc::bar_arrive(bar + 1 + RT_TC_NBUF + b);
                     }
                     const uint32_t w0 = c * (RT_TC_CHUNK / 32) + i;
-                    const uint32_t m0 = tc::sign_mask(v0);
+                    const uint32_t m0 = tc::sign_mask<0>(v0);
+#if RT_TC_INLINE_PASS2
+                    // pass 2 right here, while the MMAs of the next tile run: this lane's candidates of these 64 columns
+                    unsigned long long mm = (unsigned long long)m0 << 32;
+                    if (two) mm |= tc::sign_mask<1>(v1);
+                    TC_T(5);
+                    while (mm) {
+                        const int lz = __clzll((long long)mm);
+                        mm &= ~(0x8000000000000000ull >> lz);
+                        const uint32_t j = (w0 << 5) + (uint32_t)lz;
+                        if (j < n) sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, ray_a, ray_inv_a, best_t, best_i);
+                    }
+                    TC_T(6);
+#else
                     if (m0) { s_mask[w0 * RT_TC_RAY_THREADS + tid] = m0; nz |= 0x80000000u >> w0; }
                     if (two) {
-                        const uint32_t m1 = tc::sign_mask(v1);
+                        const uint32_t m1 = tc::sign_mask<1>(v1);
                         if (m1) { s_mask[(w0 + 1u) * RT_TC_RAY_THREADS + tid] = m1; nz |= 0x80000000u >> (w0 + 1u); }
                     }
                     TC_T(5);
+#endif
                 }
+#else
+#pragma unroll
+                for (uint32_t i = 0; i < RT_TC_CHUNK / 32; ++i) {              // 32 columns at a time (register budget)
+                    uint32_t v0[32];
+                    RT_TC_LD32(v0, tmem_d + b * RT_TC_CHUNK + i * 32u);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    TC_T(4);
+                    if (i + 1 == RT_TC_CHUNK / 32) {  // the whole tile is in registers: hand the buffer back
+                        tc::fence_before();
+                        __syncwarp();
+                        if (lane == 0) tc::bar_arrive(bar + 1 + RT_TC_NBUF + b);
+                    }
+                    const uint32_t w0 = c * (RT_TC_CHUNK / 32) + i;
+                    const uint32_t m0 = (i & 1u) ? tc::sign_mask<1>(v0) : tc::sign_mask<0>(v0);
+                    if (m0) { s_mask[w0 * RT_TC_RAY_THREADS + tid] = m0; nz |= 0x80000000u >> w0; }
+                    TC_T(5);
+                }
+#endif
             }
             // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
-            best_t = FLT_MAX; best_i = -1;
             {
-                const float a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
-                const float inv_a = __frcp_rn(a);
+                const float a = ray_a, inv_a = ray_inv_a;
+#if !(RT_TC_INLINE_PASS2 && RT_TC_MASKMODE == 0)
                 uint32_t words = live ? nz : 0u, cand = 0u, w = 0u;
                 for (;;) {
                     if (cand == 0u) {
@@ -333,6 +416,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                     const uint32_t j = (w << 5) + (uint32_t)lz;
                     if (j < n) sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a, best_t, best_i);
                 }
+#endif
                 if (A.check && live) {              // self-check: the same test over all spheres must agree
                     float ct = FLT_MAX; int ci = -1;
                     for (uint32_t j = 0; j < n; ++j)

@@ -105,10 +105,21 @@ cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaS
 #define RT_TC_WGS 4
 #endif
 #ifndef RT_TC_CHUNK
-#define RT_TC_CHUNK 96
+#define RT_TC_CHUNK 64
 #endif
 #ifndef RT_TC_NBUF
 #define RT_TC_NBUF 1
+#endif
+#ifndef RT_TC_INLINE_PASS2
+#define RT_TC_INLINE_PASS2 0       // 1: run the candidate tests of a tile right after its sign masks (overlaps the next tile's MMAs)
+#endif
+#ifndef RT_TC_MASKMODE
+#define RT_TC_MASKMODE 0          // sign-mask reduction of the accumulators (tc::sign_mask): 0 I2IP, 1 FMA pipe, 2 ALU pipe, 3 both
+#endif
+#if RT_TC_MASKMODE == 0
+#define RT_TC_NEG 1.f             // accumulators hold +q, columns permuted to the I2IP bit order
+#else
+#define RT_TC_NEG -1.f            // accumulators hold -q (sign bit = candidate), columns in sphere order
 #endif
 #define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
 #define RT_TC_MIN_SPHERES 48u

@@ -228,11 +228,11 @@ def random_scene(n, seed, W, H):
     return scenes.Scene(f"random{n}", sph, mat, sc.materials, sc.mat_kind, sc.camera)
 
 
-@pytest.mark.parametrize("n", [48, 95, 96, 97, 192, 193, 488, 777, 1024])
+@pytest.mark.parametrize("n", [48, 63, 64, 65, 128, 129, 488, 777, 1024])
 def test_tensor_filter_never_drops_a_hit(be, n):
     """RT_FLAG_FILTER_CHECK re-runs the candidate test over ALL spheres for every segment and counts the
     segments whose closest hit differs from the filtered one: the tcgen05 filter is a superset filter, so 0.
-    Sphere counts straddle the 96-column accumulator tiles and the 1024-sphere limit of the tensor path."""
+    Sphere counts straddle the 64-column accumulator tiles and the 1024-sphere limit of the tensor path."""
     W, H = 192, 108
     sc = scenes.huge_scene(W, H) if n == 488 else random_scene(n, 1000 + n, W, H)
     setup(be, sc, W, H)
