@@ -329,7 +329,7 @@ def run_gpu_arm(args):
         traffic = None
         prof = os.path.join(ROOT, "profiles", "ncu_summary.json")
         kname = "k_render_tc" if finfo["tensor"] else "k_render"
-        if os.path.exists(prof):
+        if os.path.exists(prof) and world == 1:      # the committed capture is of the N=1 workload's launch
             try:
                 traffic = json.load(open(prof)).get(kname, {}).get("dram_bytes_per_launch")
             except Exception:
