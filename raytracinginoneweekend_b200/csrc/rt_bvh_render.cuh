@@ -1,0 +1,105 @@
+// rt_bvh_render.cuh -- persistent bounce loop over the GPU-built LBVH with a RESUMABLE traversal.
+// Included by rt_device.cuh in both arithmetic builds.
+//
+// Traversal lengths are heavy tailed (sky rays leave after a handful of nodes, rays that skim the sphere field visit
+// hundreds), so "every lane traverses its ray to the end, then the warp shades" keeps 6 of 32 lanes busy (ncu,
+// profiles/r01_ncu_k_render_lbvh.json).  Here the traversal state (node, stack, running closest hit) lives across
+// passes: the warp steps all traversals one node at a time and leaves the loop as soon as RT_BVH_IDLE lanes have
+// finished; those lanes are shaded / regenerated (the others "hold"), start their next traversal, and the loop resumes.
+// The stack lives in shared memory ([depth][thread], conflict free); depths beyond RT_BVH_SMEM_DEPTH (never seen on
+// Morton trees of the test scenes) go to a local-memory overflow so the result never depends on the stack size.
+// Semantics are those of closest_hit_lbvh (conservative boxes, reference test at the leaves, (t, index) order).
+#pragma once
+
+#ifndef RT_BVH_IDLE
+#define RT_BVH_IDLE 24           // leave the traversal loop when this many lanes wait for shading
+#endif
+#define RT_BVH_SMEM_DEPTH 40
+#define RT_BVH_OVF_DEPTH 64
+
+struct BvhTrav {
+    uint32_t node;
+    int sp;
+    float best_t; int best_i;
+    float a, ix, iy, iz;
+    bool active;
+};
+
+__global__ void __launch_bounds__(RT_THREADS, 3) k_render_bvh(const __grid_constant__ RtRenderArgs A)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint32_t *s_stack = reinterpret_cast<uint32_t *>(smem_raw);           // [RT_BVH_SMEM_DEPTH][RT_THREADS]
+    const RtDeviceScene &sc = A.sc;
+    const uint32_t tid = threadIdx.x;
+
+    PathSlot S;
+    S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
+    S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
+    S.ar = S.ag = S.ab = 1.f;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+    ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
+    BvhTrav T;
+    T.node = 0; T.sp = 0; T.best_t = FLT_MAX; T.best_i = -1; T.a = 0.f; T.ix = T.iy = T.iz = 0.f; T.active = false;
+    uint32_t ovf[RT_BVH_OVF_DEPTH];
+
+    for (;;) {
+        // ---- shade the lanes whose query finished, hand out new work, start their next query
+        const bool hold = T.active;
+        shade_slot<true>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
+        if (!hold) {
+            T.best_t = FLT_MAX; T.best_i = -1;
+            if (S.st == ST_ACTIVE) {
+                T.a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+                if (T.a > 0.f && T.a < 3.0e38f) {       // d = 0 or non-finite: the reference test finds nothing
+                    T.ix = 1.f / S.dx; T.iy = 1.f / S.dy; T.iz = 1.f / S.dz;
+                    T.node = sc.bvh_root; T.sp = 0; T.active = true;
+                }
+            }
+        }
+        if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
+
+        // ---- step all running traversals, one node per iteration
+        for (;;) {
+            const uint32_t act = __ballot_sync(RT_FULL, T.active);
+            if (act == 0u) break;
+            // lanes that could do something else: finished query, or a free slot while the pool still has work
+            const uint32_t idle = __ballot_sync(RT_FULL, !T.active && (S.st != ST_EMPTY || !pool.exhausted));
+            if (__popc(idle) >= RT_BVH_IDLE) break;
+            if (T.active) {
+                const float4 *np = sc.bvh_nodes + 4 * (size_t)T.node;
+                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+                ++ts.bvh.nodes;
+                const uint32_t left = __float_as_uint(n3.x), right = __float_as_uint(n3.y);
+                float tl, tr;
+                bool hl = bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tl);
+                bool hr = bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tr);
+                if (hl && (left & 0x80000000u)) { bvh_leaf(sc, left, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh); hl = false; }
+                if (hr && (right & 0x80000000u)) { bvh_leaf(sc, right, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh); hr = false; }
+                if (hl && hr) {                                   // both inner: near child first, far child on the stack
+                    const bool left_first = tl <= tr;
+                    const uint32_t far = left_first ? right : left;
+                    if (T.sp < RT_BVH_SMEM_DEPTH) s_stack[T.sp * RT_THREADS + tid] = far;
+                    else ovf[min(T.sp - RT_BVH_SMEM_DEPTH, RT_BVH_OVF_DEPTH - 1)] = far;
+                    ++T.sp;
+                    T.node = left_first ? left : right;
+                } else if (hl) T.node = left;
+                else if (hr) T.node = right;
+                else if (T.sp == 0) T.active = false;
+                else {
+                    --T.sp;
+                    T.node = (T.sp < RT_BVH_SMEM_DEPTH) ? s_stack[T.sp * RT_THREADS + tid]
+                                                         : ovf[min(T.sp - RT_BVH_SMEM_DEPTH, RT_BVH_OVF_DEPTH - 1)];
+                }
+            }
+        }
+    }
+
+    uint32_t v[7] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped, ts.bvh.nodes, ts.bvh.leaves};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        uint32_t x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
+        if ((threadIdx.x & 31u) == 0 && x) atomicAdd(A.stats + k, (unsigned long long)x);
+    }
+}

@@ -530,17 +530,19 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
 template <bool LBVH>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
-                                           float best_t, int best_i, WarpPool &pool, ThreadStats &ts)
+                                           float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false)
 {
+    // hold: this lane's closest-hit query is still running (resumable LBVH traversal); it only takes part in the
+    // warp-cooperative work pool and leaves its path untouched
     const RtDeviceScene &sc = A.sc;
-    bool want = (S.st != ST_ACTIVE);
+    bool want = !hold && (S.st != ST_ACTIVE);
     int mode = RM_NONE;
     int kind = -1;
     f3 p = mk3(0, 0, 0), n = mk3(0, 0, 0), unit = mk3(0, 0, 0), refl = mk3(0, 0, 0), refr = mk3(0, 0, 0);
     float4 m = make_float4(0, 0, 0, 0);
     float prob = 1.f;
 
-    if (S.st == ST_ACTIVE) {
+    if (!hold && S.st == ST_ACTIVE) {
         ++ts.segments;
         unit = normalize3(mk3(S.dx, S.dy, S.dz));                        // ray::unit_direction, src/math.hxx:351
         if (best_i < 0) {                                                // miss: src/main.cxx:71 (quirk F6: + 1.f)
@@ -777,6 +779,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
 #if !RT_EXACT
 #include "rt_tensor.cuh"
 #endif
+#include "rt_bvh_render.cuh"
 
 // ------------------------------------------------------------------ parity pass: primary / caller-supplied rays
 // One thread per ray; the same two-pass brute-force closest hit.  Primary rays: u = x/W, v = y/H, lens
