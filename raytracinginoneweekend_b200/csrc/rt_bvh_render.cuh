@@ -14,6 +14,12 @@
 #ifndef RT_BVH_IDLE
 #define RT_BVH_IDLE 24           // leave the traversal loop when this many lanes wait for shading
 #endif
+#ifndef RT_BVH_CTAS
+#define RT_BVH_CTAS 4
+#endif
+#ifndef RT_BVH_STEPS
+#define RT_BVH_STEPS 2              // node steps between two exit votes
+#endif
 #define RT_BVH_SMEM_DEPTH 40
 #define RT_BVH_OVF_DEPTH 64
 
@@ -25,7 +31,7 @@ struct BvhTrav {
     bool active;
 };
 
-__global__ void __launch_bounds__(RT_THREADS, 3) k_render_bvh(const __grid_constant__ RtRenderArgs A)
+__global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint32_t *s_stack = reinterpret_cast<uint32_t *>(smem_raw);           // [RT_BVH_SMEM_DEPTH][RT_THREADS]
@@ -59,31 +65,37 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render_bvh(const __grid_const
         if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
 
         // ---- step all running traversals, one node per iteration
+        // lanes that could do something else once their query ends: a live path, or a free slot while work remains
+        const uint32_t refill = __ballot_sync(RT_FULL, S.st != ST_EMPTY || !pool.exhausted);
         for (;;) {
             const uint32_t act = __ballot_sync(RT_FULL, T.active);
-            if (act == 0u) break;
-            // lanes that could do something else: finished query, or a free slot while the pool still has work
-            const uint32_t idle = __ballot_sync(RT_FULL, !T.active && (S.st != ST_EMPTY || !pool.exhausted));
-            if (__popc(idle) >= RT_BVH_IDLE) break;
-            if (T.active) {
+            if (act == 0u || __popc(~act & refill) >= RT_BVH_IDLE) break;
+#pragma unroll
+            for (int step = 0; step < RT_BVH_STEPS; ++step) {
+                if (!T.active) continue;
                 const float4 *np = sc.bvh_nodes + 4 * (size_t)T.node;
-                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+                const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(np + 3));
                 ++ts.bvh.nodes;
-                const uint32_t left = __float_as_uint(n3.x), right = __float_as_uint(n3.y);
                 float tl, tr;
                 bool hl = bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tl);
                 bool hr = bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tr);
-                if (hl && (left & 0x80000000u)) { bvh_leaf(sc, left, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh); hl = false; }
-                if (hr && (right & 0x80000000u)) { bvh_leaf(sc, right, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh); hr = false; }
-                if (hl && hr) {                                   // both inner: near child first, far child on the stack
-                    const bool left_first = tl <= tr;
-                    const uint32_t far = left_first ? right : left;
+                const bool ll = hl && (ch.x >> 31), lr = hr && (ch.y >> 31);
+                if (ll || lr) {                                   // one divergent region for both leaf children
+                    if (ll) bvh_leaf(sc, ch.x, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
+                    if (lr) bvh_leaf(sc, ch.y, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
+                }
+                hl = hl && !(ch.x >> 31); hr = hr && !(ch.y >> 31);
+                // next node by selects: near inner child, far one on the stack; nothing to enter -> pop
+                const bool left_first = tl <= tr;
+                const bool go_left = hl && (!hr || left_first);
+                if (hl && hr) {
+                    const uint32_t far = left_first ? ch.y : ch.x;
                     if (T.sp < RT_BVH_SMEM_DEPTH) s_stack[T.sp * RT_THREADS + tid] = far;
                     else ovf[min(T.sp - RT_BVH_SMEM_DEPTH, RT_BVH_OVF_DEPTH - 1)] = far;
                     ++T.sp;
-                    T.node = left_first ? left : right;
-                } else if (hl) T.node = left;
-                else if (hr) T.node = right;
+                }
+                if (hl || hr) T.node = go_left ? ch.x : ch.y;
                 else if (T.sp == 0) T.active = false;
                 else {
                     --T.sp;

@@ -427,14 +427,16 @@ __device__ __forceinline__ bool bvh_box(float lox, float loy, float loz, float h
                                         float ox, float oy, float oz, float ix, float iy, float iz,
                                         float pad0, float best_t, float &tnear)
 {
-    float far = fmaxf(fabsf(ox - lox), fabsf(ox - hix)) + fmaxf(fabsf(oy - loy), fabsf(oy - hiy)) +
-                fmaxf(fabsf(oz - loz), fabsf(oz - hiz));
+    // offsets of the six planes from the origin, shared by the pad bound and the slab test (their rounding, at most
+    // 2^-24 of `far`, disappears in the 2^-10 pad)
+    const float dlx = lox - ox, dhx = hix - ox, dly = loy - oy, dhy = hiy - oy, dlz = loz - oz, dhz = hiz - oz;
+    float far = fmaxf(fabsf(dlx), fabsf(dhx)) + fmaxf(fabsf(dly), fabsf(dhy)) + fmaxf(fabsf(dlz), fabsf(dhz));
     float pad = fmaf(far, 9.765625e-4f, pad0);
-    float t0 = (lox - pad - ox) * ix, t1 = (hix + pad - ox) * ix;
+    float t0 = (dlx - pad) * ix, t1 = (dhx + pad) * ix;
     float tn = fminf(t0, t1), tf = fmaxf(t0, t1);
-    t0 = (loy - pad - oy) * iy; t1 = (hiy + pad - oy) * iy;
+    t0 = (dly - pad) * iy; t1 = (dhy + pad) * iy;
     tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
-    t0 = (loz - pad - oz) * iz; t1 = (hiz + pad - oz) * iz;
+    t0 = (dlz - pad) * iz; t1 = (dhz + pad) * iz;
     tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
     tnear = tn;
     // relative slack on both ends; a negative tnear (origin inside) passes trivially

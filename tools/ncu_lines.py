@@ -30,3 +30,9 @@ for f, b in byfile.items(): print(f, f"inst {b[0]/tote*100:.1f}% samples {b[2]/t
 print('--- top lines by stall samples')
 for (f, l), a in sorted(agg.items(), key=lambda x: -x[1][2])[:top]:
     print(f"{f}:{l:4d} inst {a[0]/tote*100:5.2f}% samples {a[2]/tots*100:5.2f}% lanes {a[1]/max(a[0],1):5.1f}")
+print('--- instruction share by 20-line block')
+blk = collections.defaultdict(lambda: [0, 0, 0])
+for (f, l), a in agg.items():
+    b = blk[(f, l // 20 * 20)]; b[0] += a[0]; b[1] += a[1]; b[2] += a[2]
+for (f, l), a in sorted(blk.items(), key=lambda x: -x[1][0])[:top]:
+    print(f"{f}:{l:4d}-{l+19:4d} inst {a[0]/tote*100:5.2f}% samples {a[2]/tots*100:5.2f}% lanes {a[1]/max(a[0],1):5.1f}")
