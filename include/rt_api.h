@@ -186,6 +186,11 @@ RT_EXPORT int rt_tf32_peak_probe(rt_ctx *ctx, double out[3]);
  * padded sphere columns per ray, K of the filter product (tf32 slots), rays resident per CTA}. */
 RT_EXPORT int rt_filter_info(rt_ctx *ctx, uint32_t out[4]);
 
+/* Test hook: n points of the throughput build's ball sampler (lens = 0: x,y,z uniform in the unit ball, the law of
+ * raytracer::random_in_unit_sphere, src/raytracer.hxx:32-43) or lens sampler (lens = 1: x,y of such a point, z = 0,
+ * as used by camera::ray, src/camera.hxx:51-53), drawn exactly as the render kernels draw them.  HOST output, n*3 floats. */
+RT_EXPORT int rt_debug_sample_ball(rt_ctx *ctx, uint64_t n, uint64_t seed, int lens, float *out_xyz);
+
 /* ---- node-level tile queue (multi-GPU dynamic tile stealing, one process per GPU) -------------
  * RT_QUEUE_SLOTS lock-free counters (one cache line each) in POSIX shared memory, shared by the ranks of
  * one node: slot r is the cursor of rank r's own tile range; a rank that runs dry steals by advancing

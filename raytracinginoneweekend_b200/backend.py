@@ -26,7 +26,7 @@ EXPORTS = [
     "rt_render_tiles",
     "rt_primary_hits", "rt_closest_hits", "rt_readback_rgb8", "rt_readback_f32", "rt_readback_accum",
     "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
-    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info",
+    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info", "rt_debug_sample_ball",
     "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
 ]
 
@@ -109,6 +109,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_fp32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     lib.rt_tf32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     lib.rt_filter_info.argtypes = [vp, C.POINTER(C.c_uint32)]
+    lib.rt_debug_sample_ball.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_float)]
     lib.rt_queue_open.argtypes = [C.POINTER(vp), C.c_char_p, i32]
     lib.rt_queue_reset.argtypes = [vp, u32, u64]
     lib.rt_queue_next.argtypes = [vp, u32, u64, C.POINTER(u64)]
@@ -283,6 +284,13 @@ class Backend:
         out = (C.c_uint32 * 4)()
         _check(self.lib, self.lib.rt_filter_info(self.ctx, out))
         return dict(tensor=bool(out[0]), columns=int(out[1]), k=int(out[2]), rays_per_cta=int(out[3]))
+
+    def sample_ball(self, n, seed=1, lens=False):
+        """n points of the throughput build's ball (or lens) sampler, (n, 3) float32."""
+        out = np.empty((int(n), 3), np.float32)
+        _check(self.lib, self.lib.rt_debug_sample_ball(self.ctx, int(n), int(seed), 1 if lens else 0,
+                                                       out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
 
     def fp32_peak_probe(self):
         out = (C.c_double * 3)()

@@ -852,6 +852,23 @@ int rt_filter_info(rt_ctx *c, uint32_t out[4])
     return RT_OK;
 }
 
+int rt_debug_sample_ball(rt_ctx *c, uint64_t n, uint64_t seed, int lens, float *out_xyz)
+{
+    if (!c || (n && !out_xyz)) return fail(RT_ERR_INVALID, "rt_debug_sample_ball: NULL argument");
+    if (n == 0) return RT_OK;
+    if (n > (1ull << 28)) return fail(RT_ERR_INVALID, "rt_debug_sample_ball: n too large");
+    CK(cudaSetDevice(c->device));
+    float *d = nullptr;
+    CK(cudaMallocAsync((void **)&d, (size_t)n * 3u * sizeof(float), c->stream));
+    cudaError_t e = rtf::launch_sample_ball(d, n, (uint32_t)seed, (uint32_t)(seed >> 32), lens, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_xyz, d, (size_t)n * 3u * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFreeAsync(d, c->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "rt_debug_sample_ball");
+    c->hs.launches += 1;
+    return RT_OK;
+}
+
 // ---------------------------------------------------------------- node-level tile queue (POSIX shm)
 struct rt_queue {
     std::atomic<uint64_t> *ctr;   // RT_QUEUE_SLOTS counters, 64-byte stride

@@ -102,6 +102,29 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 __device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f; }
 __device__ __forceinline__ float s11(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f * 2.f + -1.f; }
 
+#if !RT_EXACT
+// Throughput build: random_in_unit_sphere (src/raytracer.hxx:32-43) by inversion instead of rejection -- the same law
+// (uniform in the unit ball) from three words: z/r uniform in [-1,1), azimuth uniform, radius U^(1/3).
+__device__ __forceinline__ void ball_by_inversion(uint32_t wz, uint32_t wphi, uint32_t wr, float &x, float &y, float &z)
+{
+    float sn, cs;
+    const float zz = s11(wz);
+    __sincosf(u01(wphi) * 6.28318548f, &sn, &cs);
+    const float rr = exp2f(__log2f(u01(wr)) * 0.333333343f);              // U^(1/3)
+    const float sxy = rr * sqrtf(fmaxf(1.f - zz * zz, 0.f));
+    x = sxy * cs; y = sxy * sn; z = rr * zz;
+}
+// x and y of such a point (all the lens offset uses, src/camera.hxx:51-53): rho = sqrt(1 - U^(2/3)), azimuth uniform.
+__device__ __forceinline__ void ball_xy_by_inversion(uint32_t wrho, uint32_t wphi, float &x, float &y)
+{
+    float sn, cs;
+    __sincosf(u01(wphi) * 6.28318548f, &sn, &cs);
+    const float q = exp2f(__log2f(u01(wrho)) * 0.666666687f);             // U^(2/3)
+    const float rho = sqrtf(fmaxf(1.f - q, 0.f));
+    x = rho * cs; y = rho * sn;
+}
+#endif
+
 // ------------------------------------------------------------------ vector math in the reference's order
 __device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 // src/math.hxx:219-227
@@ -342,6 +365,17 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
     }
     const uint32_t nthreads = blockDim.x;
     const uint32_t n = sc.n, nfilt = sc.nfilt;
+    if (n <= RT_SMALL_SCENE) {                       // a handful of spheres: the candidate test on each one costs less than one filter group
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+            const float inv_a = __frcp_rn(a);
+            if (live[r] && a > 0.f && a < 3.0e38f)
+                for (uint32_t j = 0; j < n; ++j)
+                    sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, best_t[r], best_i[r]);
+        }
+        return;
+    }
     for (uint32_t chunk = 0; chunk < nfilt; chunk += RT_FGROUP * RT_FCHUNK_WORDS) {
         const uint32_t nwords = min((uint32_t)RT_FCHUNK_WORDS, (nfilt - chunk) / RT_FGROUP);
         for (uint32_t w = 0; w < nwords; ++w) {
@@ -665,21 +699,12 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     const bool camera_lane = (mode == RM_CAMERA);
     if (mode != RM_NONE) {
         const uint4 w = philox4x32_10(S.pix, S.smp, ev, 0u, A.key0, A.key1);
-        const float c13 = 0.333333343f;
-        float sn, cs;
         if (camera_lane) {
             ju = u01(w.x); jv = u01(w.y);
-            __sincosf(u01(w.w) * 6.28318548f, &sn, &cs);
-            const float q = exp2f(__log2f(u01(w.z)) * (2.f * c13));       // U^(2/3)
-            const float rho = sqrtf(fmaxf(1.f - q, 0.f));
-            r0 = rho * cs; r1 = rho * sn;
+            ball_xy_by_inversion(w.z, w.w, r0, r1);
         } else {
-            const float z = s11(w.x);
-            __sincosf(u01(w.y) * 6.28318548f, &sn, &cs);
-            const float rr = exp2f(__log2f(u01(w.z)) * c13);              // U^(1/3)
-            const float sxy = rr * sqrtf(fmaxf(1.f - z * z, 0.f));
-            r0 = (mode == RM_UNIFORM) ? u01(w.x) : sxy * cs;              // the dielectric coin is word 0, as in the parity build
-            r1 = sxy * sn; r2 = rr * z;
+            ball_by_inversion(w.x, w.y, w.z, r0, r1, r2);
+            if (mode == RM_UNIFORM) r0 = u01(w.x);                        // the dielectric coin is word 0, as in the parity build
         }
     }
 #endif
@@ -718,6 +743,21 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         }
     }
 }
+
+#if !RT_EXACT
+// Sampler dump for the distribution tests (tests/test_gpu_parity.py): point i of the ball sampler (lens = 0) or of the
+// lens sampler (lens = 1: x, y, 0) exactly as shade_slot draws them, from Philox block (i, 0, event 1, 0).
+__global__ void k_sample_ball(float *out, unsigned long long n, uint32_t key0, uint32_t key1, int lens)
+{
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 w = philox4x32_10((uint32_t)i, (uint32_t)(i >> 32), 1u, 0u, key0, key1);
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (lens) ball_xy_by_inversion(w.z, w.w, x, y);
+    else ball_by_inversion(w.x, w.y, w.z, x, y, z);
+    out[3 * i + 0] = x; out[3 * i + 1] = y; out[3 * i + 2] = z;
+}
+#endif
 
 template <bool LBVH, bool CHECK = false>
 __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant__ RtRenderArgs A)

@@ -99,8 +99,12 @@ cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 
 namespace rtf {
 cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, uint32_t key1, int lens, cudaStream_t s);
 }
 // tensor-filter kernel shape (rt_tensor.cuh): RT_TC_WGS ray warpgroups x (32 + RT_TC_NBUF * RT_TC_CHUNK) TMEM columns <= 512
+#ifndef RT_SMALL_SCENE
+#define RT_SMALL_SCENE 12u    // throughput build: at or below this many spheres the closest hit tests every sphere directly (no filter)
+#endif
 #ifndef RT_TC_WGS
 #define RT_TC_WGS 4
 #endif

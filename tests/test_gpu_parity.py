@@ -215,6 +215,45 @@ def test_fast_and_exact_builds_agree_statistically(be):
 
 
 # ------------------------------------------------------------------ tensor-core candidate filter (throughput build)
+def reference_ball_numpy(n, seed):
+    """random_in_unit_sphere restated in numpy (src/raytracer.hxx:32-43): 3 x U(-1,1) until length <= 1."""
+    rng = np.random.default_rng(seed)
+    out = np.empty((0, 3), np.float32)
+    while len(out) < n:
+        v = rng.uniform(-1.0, 1.0, size=(2 * n, 3)).astype(np.float32)
+        out = np.concatenate([out, v[np.sqrt((v * v).sum(1)) <= 1.0]])
+    return out[:n]
+
+
+@pytest.mark.parametrize("lens", [False, True], ids=["ball", "lens"])
+def test_inversion_sampler_has_the_law_of_the_rejection_sampler(be, lens):
+    """The throughput build draws random_in_unit_sphere by inversion (one Philox block) instead of the reference's
+    rejection loop.  Same law: checked against the closed-form CDFs and, two-sample, against the rejection loop."""
+    from scipy import stats
+    n = 1 << 20
+    p = be.sample_ball(n, seed=12345, lens=lens).astype(np.float64)
+    ref = reference_ball_numpy(n, 7).astype(np.float64)
+    if lens:
+        assert np.all(p[:, 2] == 0.0)
+        ref = ref.copy(); ref[:, 2] = 0.0
+        rho = np.hypot(p[:, 0], p[:, 1])
+        assert rho.max() <= 1.0 + 1e-6
+        assert stats.kstest(rho, lambda t: 1.0 - (1.0 - np.clip(t, 0, 1) ** 2) ** 1.5).pvalue > 1e-4
+    else:
+        r = np.sqrt((p * p).sum(1))
+        assert r.max() <= 1.0 + 1e-6
+        assert stats.kstest(r, lambda t: np.clip(t, 0, 1) ** 3).pvalue > 1e-4           # volume grows as r^3
+        assert stats.kstest(p[:, 2] / np.maximum(r, 1e-30), stats.uniform(-1, 2).cdf).pvalue > 1e-4
+        assert abs((p * p).sum(1).mean() - 0.6) < 2e-3                                   # E r^2 = 3/5
+    phi = np.arctan2(p[:, 1], p[:, 0])
+    assert stats.kstest(phi, stats.uniform(-np.pi, 2 * np.pi).cdf).pvalue > 1e-4
+    for k in range(2 if lens else 3):                                                    # marginals against the rejection loop
+        assert stats.ks_2samp(p[:, k], ref[:, k]).pvalue > 1e-4, k
+        assert abs(p[:, k].mean()) < 3e-3 and abs((p[:, k] ** 2).mean() - 0.2) < 2e-3
+    c = np.corrcoef(p[:, :2].T)[0, 1]
+    assert abs(c) < 5e-3
+
+
 def random_scene(n, seed, W, H):
     """n spheres of mixed sizes and materials around the camera's view, plus a huge ground sphere when n > 3."""
     rng = np.random.default_rng(seed)
