@@ -170,6 +170,18 @@ RT_EXPORT int rt_render_frame(rt_ctx *ctx, const rt_sphere *spheres, uint32_t n,
                               uint32_t width, uint32_t height, const rt_render_params *params,
                               uint8_t *rgb8_out);
 
+/* Progressive rendering: trace params->spp paths per pixel over the whole framebuffer in passes of spp_per_pass
+ * (samples [sample_base + k*spp_per_pass, ...), so the accumulators end bit-identical to one rt_render of params->spp --
+ * the split accumulation of src/main.cxx:205-207).  After every `preview_every`-th pass the image of the samples so far
+ * is resolved, copied to pinned host memory on a second stream and handed to `preview` WHILE the next pass renders;
+ * the final image is written to rgb8_out (HOST, W*H*3; may be NULL) and passed to the callback too.  The callback's
+ * rgb8 pointer is valid only during the call; returning non-zero stops after the pass in flight (RT_OK is returned,
+ * *spp_done tells how far it got).  preview == NULL or preview_every == 0: no previews. */
+typedef int (*rt_preview_fn)(void *user, uint32_t pass, uint32_t spp_done, const uint8_t *rgb8);
+RT_EXPORT int rt_render_progressive(rt_ctx *ctx, const rt_render_params *params, uint32_t spp_per_pass,
+                                    uint32_t preview_every, rt_preview_fn preview, void *user, uint8_t *rgb8_out,
+                                    uint32_t *spp_done);
+
 RT_EXPORT int rt_stats_get(rt_ctx *ctx, rt_stats *out);
 RT_EXPORT int rt_stats_reset(rt_ctx *ctx);
 

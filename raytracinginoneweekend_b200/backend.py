@@ -26,7 +26,7 @@ EXPORTS = [
     "rt_render_tiles",
     "rt_primary_hits", "rt_closest_hits", "rt_readback_rgb8", "rt_readback_f32", "rt_readback_accum",
     "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
-    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info", "rt_debug_sample_ball",
+    "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info", "rt_debug_sample_ball", "rt_render_progressive",
     "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
 ]
 
@@ -60,6 +60,9 @@ class RtStats(C.Structure):
 
 SPHERE_DTYPE = np.dtype([("cx", "<f4"), ("cy", "<f4"), ("cz", "<f4"), ("r", "<f4"), ("mat", "<u4")])
 MATERIAL_DTYPE = np.dtype([("r", "<f4"), ("g", "<f4"), ("b", "<f4"), ("param", "<f4"), ("kind", "<u4")])
+
+
+PREVIEW_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint8))
 
 
 class RtError(RuntimeError):
@@ -109,6 +112,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_fp32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     lib.rt_tf32_peak_probe.argtypes = [vp, C.POINTER(C.c_double)]
     lib.rt_filter_info.argtypes = [vp, C.POINTER(C.c_uint32)]
+    lib.rt_render_progressive.argtypes = [vp, C.POINTER(RtRenderParams), u32, u32, PREVIEW_FN, vp, vp, C.POINTER(u32)]
     lib.rt_debug_sample_ball.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_float)]
     lib.rt_queue_open.argtypes = [C.POINTER(vp), C.c_char_p, i32]
     lib.rt_queue_reset.argtypes = [vp, u32, u64]
@@ -267,6 +271,30 @@ class Backend:
         return out
 
     # ---- statistics / probes ------------------------------------------------
+    def render_progressive(self, spp, spp_per_pass, preview_every=1, on_preview=None, max_depth=50, seed=1,
+                           sample_base=0, flags=0):
+        """rt_render_progressive: on_preview(pass_index, spp_done, image[H,W,3] uint8) -> truthy to stop.
+        Returns (final image, spp_done)."""
+        W, H = self.W, self.H
+        out = np.empty((H, W, 3), np.uint8)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
+        err = []
+
+        def tramp(_user, npass, done, ptr):
+            try:
+                img = np.ctypeslib.as_array(ptr, shape=(H, W, 3))
+                return 1 if on_preview(int(npass), int(done), img) else 0
+            except BaseException as ex:   # never unwind through the C frame
+                err.append(ex)
+                return 1
+        cb = PREVIEW_FN(tramp) if on_preview else PREVIEW_FN(0)
+        done = C.c_uint32(0)
+        _check(self.lib, self.lib.rt_render_progressive(self.ctx, C.byref(p), int(spp_per_pass), int(preview_every), cb, None,
+                                                        out.ctypes.data_as(C.c_void_p), C.byref(done)))
+        if err:
+            raise err[0]
+        return out, int(done.value)
+
     def stats(self):
         s = RtStats()
         _check(self.lib, self.lib.rt_stats_get(self.ctx, C.byref(s)))

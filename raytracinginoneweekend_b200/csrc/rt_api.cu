@@ -745,6 +745,91 @@ int rt_render_frame(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
     return rt_readback_rgb8(c, rgb8_out);
 }
 
+// Progressive rendering: the accumulation of src/main.cxx:205-207 split into passes, with previews
+// streamed to the host while the next pass renders.
+//   render stream : [pass k] [resolve -> preview buffer i] (event R_i) [pass k+1] ...
+//   copy stream   : wait R_i, D2H preview buffer i -> pinned buffer i (event C_i)
+//   host          : enqueue pass k+1 first, then wait C_i and hand pinned buffer i to the callback
+// The resolve runs in stream order between two passes, so a preview is exactly the image of the samples so far (never a
+// torn mix with the pass that follows); two device + two pinned buffers let copy and callback overlap the rendering.
+int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per_pass, uint32_t preview_every,
+                          rt_preview_fn cb, void *user, uint8_t *rgb8_out, uint32_t *spp_done_out)
+{
+    if (!c || !p) return fail(RT_ERR_INVALID, "rt_render_progressive: NULL argument");
+    if (spp_per_pass == 0) return fail(RT_ERR_INVALID, "rt_render_progressive: spp_per_pass must be > 0");
+    if (!c->d_sph || !c->have_cam || !c->d_accum)
+        return fail(RT_ERR_INVALID, "rt_render_progressive: scene, camera and framebuffer must be set first");
+    CK(cudaSetDevice(c->device));
+    const size_t bytes = (size_t)c->W * c->H * 3;
+    const bool previews = cb && preview_every > 0;
+    unsigned char *d_prev[2] = {nullptr, nullptr};
+    unsigned char *h_prev[2] = {nullptr, nullptr};
+    cudaStream_t copy = nullptr;
+    cudaEvent_t R[2] = {nullptr, nullptr}, Cv[2] = {nullptr, nullptr};
+    int rc = RT_OK;
+    cudaError_t e = cudaSuccess;
+    auto cleanup = [&]() {
+        if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
+        for (int i = 0; i < 2; ++i) {
+            if (d_prev[i]) cudaFree(d_prev[i]);
+            if (h_prev[i]) cudaFreeHost(h_prev[i]);
+            if (R[i]) cudaEventDestroy(R[i]);
+            if (Cv[i]) cudaEventDestroy(Cv[i]);
+        }
+    };
+    if (previews) {
+        e = cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking);
+        for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+            e = cudaMalloc((void **)&d_prev[i], bytes);
+            if (e == cudaSuccess) e = cudaMallocHost((void **)&h_prev[i], bytes);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&R[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&Cv[i], cudaEventDisableTiming);
+        }
+        if (e != cudaSuccess) { cleanup(); return cuda_fail(e, "rt_render_progressive: preview buffers"); }
+    }
+    const rt_tile full = {0, 0, c->W, c->H};
+    uint32_t done = 0, pass = 0, nprev = 0;
+    int pending = -1; uint32_t pending_pass = 0, pending_spp = 0;     // preview in flight: buffer index, its pass and sample count
+    bool stop = false;
+    auto deliver = [&]() -> int {                                    // wait for the copy of the pending preview and call back
+        if (pending < 0) return RT_OK;
+        cudaError_t ee = cudaEventSynchronize(Cv[pending]);
+        if (ee != cudaSuccess) return cuda_fail(ee, "rt_render_progressive: preview copy");
+        if (cb(user, pending_pass, pending_spp, h_prev[pending]) != 0) stop = true;
+        pending = -1;
+        return RT_OK;
+    };
+    while (done < p->spp && !stop) {
+        rt_render_params q = *p;
+        q.spp = (p->spp - done < spp_per_pass) ? (p->spp - done) : spp_per_pass;
+        q.sample_base = p->sample_base + done;
+        rc = rt_render(c, &full, &q);
+        if (rc) break;
+        done += q.spp; ++pass;
+        // the previous preview is delivered while this pass runs on the GPU
+        rc = deliver();
+        if (rc) break;
+        if (previews && !stop && (pass % preview_every == 0) && done < p->spp) {
+            const int i = (int)(nprev & 1u);
+            e = rt_launch_resolve(c->d_accum, (unsigned long long)c->W * c->H, d_prev[i], nullptr, c->stream);
+            if (e == cudaSuccess) e = cudaEventRecord(R[i], c->stream);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(copy, R[i], 0);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(h_prev[i], d_prev[i], bytes, cudaMemcpyDeviceToHost, copy);
+            if (e == cudaSuccess) e = cudaEventRecord(Cv[i], copy);
+            if (e != cudaSuccess) { rc = cuda_fail(e, "rt_render_progressive: preview"); break; }
+            c->hs.launches += 1;
+            pending = i; pending_pass = pass; pending_spp = done; ++nprev;
+        }
+    }
+    if (rc == RT_OK && !stop) rc = deliver();                        // a preview taken before the last pass
+    if (spp_done_out) *spp_done_out = done;
+    if (rc == RT_OK && rgb8_out) rc = rt_readback_rgb8(c, rgb8_out); // final image of everything accumulated
+    else if (rc == RT_OK) { cudaError_t ee = cudaStreamSynchronize(c->stream); if (ee != cudaSuccess) rc = cuda_fail(ee, "rt_render_progressive"); }
+    if (rc == RT_OK && cb && !stop && rgb8_out) cb(user, pass, done, rgb8_out);   // the final image also goes through the callback
+    cleanup();
+    return rc;
+}
+
 int rt_stats_get(rt_ctx *c, rt_stats *out)
 {
     if (!c || !out) return fail(RT_ERR_INVALID, "rt_stats_get: NULL argument");

@@ -328,6 +328,52 @@ def test_render_frame_equals_staged_calls(be):
 
 
 # ------------------------------------------------------------------ edge cases and error behaviour
+def test_progressive_render_equals_one_shot_and_previews_are_exact(be):
+    """rt_render_progressive: the accumulators after all passes are bit-identical to one rt_render of the total spp
+    (integer accumulation is order independent), every preview is exactly the image of the samples so far, previews
+    arrive while later passes render, and a callback can stop the render."""
+    W, H = 160, 90
+    sc = scenes.huge_scene(W, H)
+    for flags in (0, FLAG_EXACT):
+        setup(be, sc, W, H)
+        be.clear()
+        be.render(12, 50, seed=3, flags=flags)
+        one_shot_acc = be.readback_accum().copy()
+        one_shot_img = be.readback_rgb8().copy()
+        partial = {}
+        for spp_done in (4, 8):
+            be.clear(); be.render(spp_done, 50, seed=3, flags=flags)
+            partial[spp_done] = be.readback_rgb8().copy()
+        be.clear()
+        seen = []
+        img, done = be.render_progressive(12, 4, preview_every=1, seed=3, flags=flags,
+                                          on_preview=lambda k, n, im: seen.append((k, n, im.copy())) and False)
+        assert done == 12
+        assert_bits_equal(be.readback_accum(), one_shot_acc, "progressive accumulators")
+        assert np.array_equal(img, one_shot_img)
+        assert [(k, n) for k, n, _ in seen] == [(1, 4), (2, 8), (3, 12)]
+        assert np.array_equal(seen[0][2], partial[4]) and np.array_equal(seen[1][2], partial[8])
+        assert np.array_equal(seen[2][2], one_shot_img)
+    # ragged last pass, sparse previews
+    be.clear()
+    seen = []
+    img, done = be.render_progressive(10, 4, preview_every=2, seed=3, on_preview=lambda k, n, im: seen.append((k, n)) and False)
+    assert done == 10 and seen == [(2, 8), (3, 10)]
+    # cancellation: stop at the first preview; at most the pass already in flight is added
+    be.clear()
+    img, done = be.render_progressive(40, 4, preview_every=1, seed=3, on_preview=lambda k, n, im: True)
+    assert done in (4, 8)
+    acc = be.readback_accum()
+    assert int(acc[..., 3].max()) == done and int(acc[..., 3].min()) == done
+    # no callback: plain multi-pass render
+    be.clear()
+    img, done = be.render_progressive(12, 5, preview_every=0, seed=3)
+    assert done == 12
+    assert int(be.readback_accum()[..., 3].min()) == 12
+    with pytest.raises(RtError):
+        be.render_progressive(4, 0)
+
+
 def test_edge_cases_and_errors(be):
     from raytracinginoneweekend_b200.backend import Backend
     sc = scenes.simple_scene(16, 9)
