@@ -58,8 +58,14 @@ enum {
     RT_FLAG_ACCEL_LBVH = 1u << 2, /* force the GPU-built LBVH */
     RT_FLAG_FILTER_FMA = 1u << 3  /* brute force, throughput build: run the candidate filter on the FP32 FMA pipe instead of
                                      the tensor cores (tcgen05 TF32x3 product, the default up to 1024 spheres); same image */,
-    RT_FLAG_FILTER_CHECK = 1u << 4/* self-check: after the filtered closest hit, run the candidate test over ALL spheres and count
+    RT_FLAG_FILTER_CHECK = 1u << 4,/* self-check: after the filtered closest hit, run the candidate test over ALL spheres and count
                                      the segments whose result differs in rt_stats.filter_misses (must stay 0; slow) */
+    RT_FLAG_BOOK_OPTICS = 1u << 5 /* opt-in, NOT the reference's picture: textbook optics in place of the reference's quirks --
+                                     Snell refraction with total internal reflection (vs src/math.hxx:300-309), camera
+                                     direction measured from the eye and a disk lens in the camera basis (vs
+                                     src/camera.hxx:46-57), sky blend .5*y + .5 (vs src/main.cxx:71).  Everything else
+                                     (closest hit, lambert/metal sampling, Schlick, accumulate, resolve) is unchanged.
+                                     rt_render / rt_render_tiles / rt_render_progressive / rt_render_frame only. */
     /* neither accel flag: brute force up to RT_BRUTE_MAX_SPHERES, LBVH above */
 };
 #define RT_BRUTE_MAX_SPHERES 8192u

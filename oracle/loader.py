@@ -22,6 +22,7 @@ REF_SO = os.path.join(HERE, "_ref", "libref_oracle.so")
 PORT_SO = os.path.join(HERE, "_build", "librt_oracle.so")
 
 RNG_MT, RNG_PHILOX = 0, 1
+OPT_BOOK = 0x100   # OR into `rng`: textbook optics (the backend's RT_FLAG_BOOK_OPTICS); not the reference's picture
 
 _f = np.float32
 fp = C.POINTER(C.c_float)

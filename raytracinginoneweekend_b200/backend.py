@@ -18,6 +18,7 @@ FLAG_EXACT = 1 << 0
 FLAG_BRUTE = 1 << 1
 FLAG_LBVH = 1 << 2
 FLAG_FILTER_CHECK = 1 << 4  # count segments whose filtered closest hit differs from the unfiltered one (stats: filter_misses)
+FLAG_BOOK_OPTICS = 1 << 5   # opt-in textbook optics (Snell refraction, eye-relative camera rays, disk lens, [0,1] sky blend)
 FLAG_FILTER_FMA = 1 << 3   # throughput build: candidate filter on the FMA pipe instead of the tensor cores
 
 EXPORTS = [

@@ -443,6 +443,8 @@ int rt_camera_set(rt_ctx *c, const float pos[3], const float lookat[3], const fl
     d.hx = hor.x; d.hy = hor.y; d.hz = hor.z;
     d.vx = ver.x; d.vy = ver.y; d.vz = ver.z;
     d.lens_radius = aperture / 2.f;
+    d.bux = u.x; d.buy = u.y; d.buz = u.z;
+    d.bvx = v.x; d.bvy = v.y; d.bvz = v.z;
     c->have_cam = true;
     return RT_OK;
 }
@@ -545,6 +547,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
     a.stats = c->d_stats;
     a.check = (p->flags & RT_FLAG_FILTER_CHECK) ? 1u : 0u;
+    a.book = (p->flags & RT_FLAG_BOOK_OPTICS) ? 1u : 0u;
 
     // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic)
     uint32_t per_band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);

@@ -123,6 +123,14 @@ __device__ __forceinline__ void ball_xy_by_inversion(uint32_t wrho, uint32_t wph
     const float rho = sqrtf(fmaxf(1.f - q, 0.f));
     x = rho * cs; y = rho * sn;
 }
+// RT_FLAG_BOOK_OPTICS lens: uniform in the unit disk.
+__device__ __forceinline__ void disk_by_inversion(uint32_t wrho, uint32_t wphi, float &x, float &y)
+{
+    float sn, cs;
+    __sincosf(u01(wphi) * 6.28318548f, &sn, &cs);
+    const float rho = sqrtf(u01(wrho));
+    x = rho * cs; y = rho * sn;
+}
 #endif
 
 // ------------------------------------------------------------------ vector math in the reference's order
@@ -157,6 +165,16 @@ __device__ __forceinline__ f3 refract3(f3 I, f3 N, float eta)
     float s = dv * eta;
     float z = (k >= 0.f) ? 1.f : 0.f;
     return mk3((I.x * eta - (N.x * sk + s)) * z, (I.y * eta - (N.y * sk + s)) * z, (I.z * eta - (N.z * sk + s)) * z);
+}
+// RT_FLAG_BOOK_OPTICS: Snell refraction (GLSL refract); k < 0 (total internal reflection) gives the zero vector, which
+// the caller (src/raytracer.hxx:175-191) turns into a certain reflection.
+__device__ __forceinline__ f3 refract3_book(f3 I, f3 N, float eta)
+{
+    float dv = dot3(N, I);
+    float k = 1.f - eta * eta * (1.f - dv * dv);
+    if (!(k >= 0.f)) return mk3(0.f, 0.f, 0.f);
+    float s = eta * dv + sqrtf(k);
+    return mk3(I.x * eta - N.x * s, I.y * eta - N.y * s, I.z * eta - N.z * s);
 }
 // src/raytracer.hxx:45-50
 __device__ __forceinline__ float schlick(float ri, float cosine)
@@ -582,7 +600,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         ++ts.segments;
         unit = normalize3(mk3(S.dx, S.dy, S.dz));                        // ray::unit_direction, src/math.hxx:351
         if (best_i < 0) {                                                // miss: src/main.cxx:71 (quirk F6: + 1.f)
-            float t = .5f * unit.y + 1.f;
+            float t = .5f * unit.y + (A.book ? .5f : 1.f);              // book optics: the usual [0,1] blend
             float omt = 1.f - t;
             float cr = (omt + .5f * t) * S.ar, cg = (omt + .7f * t) * S.ag, cb = (omt + 1.f * t) * S.ab;
             unsigned long long *px = A.accum + 4ull * S.pix;
@@ -618,7 +636,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
                     ri = 1.f / ri;
                     cosine = cosine * -1.f;
                 }
-                refr = refract3(unit, outward, ri);
+                refr = A.book ? refract3_book(unit, outward, ri) : refract3(unit, outward, ri);
                 if (refr.x * refr.x + refr.y * refr.y + refr.z * refr.z > 0.f) prob = schlick(ri, cosine);
                 refl = reflect3(unit, n);
                 mode = RM_UNIFORM;
@@ -678,6 +696,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             mode = RM_NONE;
         } else {                                                          // src/raytracer.hxx:32-43
             r0 = s11(w.x); r1 = s11(w.y); r2 = s11(w.z);
+            if (camera_lane && A.book) r2 = 0.f;                          // book optics: the lens sample is a DISK point
 #if RT_EXACT
             bool reject = sqrtf(r0 * r0 + r1 * r1 + r2 * r2) > 1.f;
 #else
@@ -701,7 +720,8 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         const uint4 w = philox4x32_10(S.pix, S.smp, ev, 0u, A.key0, A.key1);
         if (camera_lane) {
             ju = u01(w.x); jv = u01(w.y);
-            ball_xy_by_inversion(w.z, w.w, r0, r1);
+            if (A.book) disk_by_inversion(w.z, w.w, r0, r1);
+            else ball_xy_by_inversion(w.z, w.w, r0, r1);
         } else {
             ball_by_inversion(w.x, w.y, w.z, r0, r1, r2);
             if (mode == RM_UNIFORM) r0 = u01(w.x);                        // the dielectric coin is word 0, as in the parity build
@@ -717,10 +737,14 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         float rdx = r0 * c.lens_radius, rdy = r1 * c.lens_radius;
         float offx = u * rdx, offy = v * rdy, offz = 0.f;
         float omv = 1.f - v;
+        if (A.book) {       // book optics: lens offset in the camera basis, direction measured from the eye (fixes F3, F4)
+            offx = c.bux * rdx + c.bvx * rdy; offy = c.buy * rdx + c.bvy * rdy; offz = c.buz * rdx + c.bvz * rdy;
+        }
         S.ox = c.ox + offx; S.oy = c.oy + offy; S.oz = c.oz + offz;
         S.dx = ((c.llx + c.hx * u) + c.vx * omv) - offx;
         S.dy = ((c.lly + c.hy * u) + c.vy * omv) - offy;
         S.dz = ((c.llz + c.hz * u) + c.vz * omv) - offz;
+        if (A.book) { S.dx = S.dx - c.ox; S.dy = S.dy - c.oy; S.dz = S.dz - c.oz; }
     } else if (kind >= 0) {
         bool scattered = true;
         f3 nd;

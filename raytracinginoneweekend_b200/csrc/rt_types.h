@@ -52,6 +52,8 @@ struct RtDeviceCamera {          // src/camera.hxx:66-76 derived state
     float hx, hy, hz;
     float vx, vy, vz;
     float lens_radius;
+    float bux, buy, buz;         // unit camera basis vectors u, v (src/camera.hxx:36-37): only the book-optics lens uses them
+    float bvx, bvy, bvz;
 };
 
 struct RtRenderArgs {
@@ -73,6 +75,7 @@ struct RtRenderArgs {
     uint32_t *work_counter;      // zeroed before launch
     unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] sphere tests [7] filter misses
     uint32_t check;              // RT_FLAG_FILTER_CHECK
+    uint32_t book;               // RT_FLAG_BOOK_OPTICS
 };
 
 struct RtHitArgs {

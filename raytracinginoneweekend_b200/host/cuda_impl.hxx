@@ -12,6 +12,7 @@
 //       the same call for a caller-supplied scene (what main() would pass if the scene were not hard-coded).
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <vector>
 #include "camera.hxx"
 #include "math.hxx"
@@ -23,6 +24,11 @@ struct cuda_impl_options final {
     std::uint64_t seed{1};
     bool exact{false};                     // parity build (no FMA contraction)
     int device{0};
+    // progressive rendering (rt_render_progressive): passes of this many samples (0 = one shot) and, every
+    // `preview_every` passes, the image so far handed to `on_preview` while the next pass renders; return true to stop
+    std::uint32_t samples_per_pass{0};
+    std::uint32_t preview_every{1};
+    std::function<bool(std::uint32_t pass, std::uint32_t samples_done, std::uint8_t const *rgb8)> on_preview{};
 };
 
 void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels);

@@ -67,10 +67,27 @@ void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8ve
     p.sample_base = 0;
     p.flags = options.exact ? static_cast<std::uint32_t>(RT_FLAG_EXACT) : 0u;
     static_assert(sizeof(math::u8vec3) == 3, "texels are tightly packed RGB8");
-    check(rt_render_frame(g.ctx, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
-                          static_cast<std::uint32_t>(materials.size()), cam13, width, height, &p,
-                          reinterpret_cast<std::uint8_t *>(image_texels.data())),
-          "rt_render_frame");
+    auto *texels = reinterpret_cast<std::uint8_t *>(image_texels.data());
+    if (options.samples_per_pass == 0) {
+        check(rt_render_frame(g.ctx, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
+                              static_cast<std::uint32_t>(materials.size()), cam13, width, height, &p, texels),
+              "rt_render_frame");
+        return;
+    }
+    check(rt_scene_upload(g.ctx, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
+                          static_cast<std::uint32_t>(materials.size())), "rt_scene_upload");
+    check(rt_camera_set(g.ctx, cam13, cam13 + 3, cam13 + 6, cam13[9], cam13[10], cam13[11], cam13[12]), "rt_camera_set");
+    check(rt_framebuffer(g.ctx, width, height), "rt_framebuffer");
+    struct relay { cuda_impl_options const *opt; std::exception_ptr error; } r{&options, nullptr};
+    auto trampoline = [](void *user, std::uint32_t pass, std::uint32_t done, std::uint8_t const *rgb8) -> int {
+        auto *rl = static_cast<relay *>(user);
+        try { return rl->opt->on_preview(pass, done, rgb8) ? 1 : 0; }
+        catch (...) { rl->error = std::current_exception(); return 1; }     // no exception crosses the C ABI
+    };
+    check(rt_render_progressive(g.ctx, &p, options.samples_per_pass, options.preview_every,
+                                options.on_preview ? static_cast<rt_preview_fn>(trampoline) : nullptr, &r, texels, nullptr),
+          "rt_render_progressive");
+    if (r.error) std::rethrow_exception(r.error);
 }
 
 void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8vec3> &image_texels)

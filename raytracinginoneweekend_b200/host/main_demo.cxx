@@ -2,6 +2,7 @@
 // cuda_impl, write a P6 PPM), with the scene, size, spp and depth on the command line.
 //   rtiow_demo [--scene simple|huge|synthetic:N] [--width W] [--height H] [--spp S] [--depth D] [--seed X]
 //              [--exact] [--out image.ppm] [--dump-scene file.bin]
+//              [--spp-per-pass P [--preview-every K] [--preview-prefix path_]]   progressive passes with previews
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -53,7 +54,7 @@ void dump_scene(scenes::scene const &sc, std::string const &path)
 
 int main(int argc, char **argv)
 {
-    std::string scene_name = "simple", out = "image_cuda.ppm", dump;
+    std::string scene_name = "simple", out = "image_cuda.ppm", dump, preview_prefix;
     std::uint32_t width = 1920, height = 1080;   // src/main.cxx:29-30
     cuda_impl_options opt;
     try {
@@ -71,6 +72,9 @@ int main(int argc, char **argv)
             else if (a == "--seed") opt.seed = std::stoull(next());
             else if (a == "--device") opt.device = std::stoi(next());
             else if (a == "--exact") opt.exact = true;
+            else if (a == "--spp-per-pass") opt.samples_per_pass = static_cast<std::uint32_t>(std::stoul(next()));
+            else if (a == "--preview-every") opt.preview_every = static_cast<std::uint32_t>(std::stoul(next()));
+            else if (a == "--preview-prefix") preview_prefix = next();
             else if (a == "--out") out = next();
             else if (a == "--dump-scene") dump = next();
             else throw std::invalid_argument("unknown option " + a);
@@ -79,6 +83,14 @@ int main(int argc, char **argv)
         auto sc = scenes::by_name(scene_name, width, height);
         if (!dump.empty()) { dump_scene(sc, dump); return 0; }
         std::vector<math::u8vec3> output(static_cast<std::size_t>(width) * height);   // src/main.cxx:112
+        if (opt.samples_per_pass) {                                    // progressive: report (and optionally save) the previews
+            opt.on_preview = [&](std::uint32_t pass, std::uint32_t done, std::uint8_t const *rgb8) {
+                std::cout << "preview: pass " << pass << ", " << done << " spp\n";
+                if (!preview_prefix.empty())
+                    rt_write_ppm((preview_prefix + std::to_string(done) + ".ppm").c_str(), width, height, rgb8);
+                return false;
+            };
+        }
         cuda_impl(width, height, output, sc.data, sc.camera, opt);
         if (rt_write_ppm(out.c_str(), width, height, reinterpret_cast<std::uint8_t const *>(output.data())) != RT_OK)
             throw std::runtime_error(rt_last_error());

@@ -13,7 +13,7 @@ import pytest
 
 from conftest import assert_bits_equal
 from raytracinginoneweekend_b200 import scenes
-from raytracinginoneweekend_b200.backend import (FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH,
+from raytracinginoneweekend_b200.backend import (FLAG_BOOK_OPTICS, FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH,
                                                  RtError)
 
 pytestmark = pytest.mark.gpu
@@ -372,6 +372,69 @@ def test_progressive_render_equals_one_shot_and_previews_are_exact(be):
     assert int(be.readback_accum()[..., 3].min()) == 12
     with pytest.raises(RtError):
         be.render_progressive(4, 0)
+
+
+# ------------------------------------------------------------------ opt-in textbook optics
+def moved_camera_scene(name, W, H):
+    """The scene with the camera NOT at the origin (all centres and the camera shifted): the reference's camera::ray
+    (quirk F3) breaks there, the book-optics ray does not."""
+    sc = scenes.get_scene(name, W, H)
+    shift = np.array([3.0, -2.0, 5.0], np.float32)
+    sph = sc.spheres.copy(); sph[:, :3] += shift
+    cam = sc.camera.copy(); cam[0:3] += shift; cam[3:6] += shift
+    return scenes.Scene(sc.name + "-moved", sph, sc.sphere_mat.copy(), sc.materials.copy(), sc.mat_kind.copy(), cam)
+
+
+@pytest.mark.parametrize("name,W,H,spp,depth", [("simple", 96, 54, 4, 50), ("huge", 64, 36, 3, 50)])
+def test_book_optics_exact_render_is_bit_identical_to_oracle(be, port, name, W, H, spp, depth):
+    """RT_FLAG_BOOK_OPTICS in the parity build == the oracle restatement with the same three substitutions
+    (Snell refraction, eye-relative camera ray with a disk lens, [0,1] sky blend), bit for bit."""
+    from oracle.loader import OPT_BOOK
+    sc = moved_camera_scene(name, W, H)
+    setup(be, sc, W, H)
+    be.clear()
+    be.render(spp, depth, seed=77, flags=FLAG_EXACT | FLAG_BOOK_OPTICS)
+    acc = be.readback_accum()
+    o = port.render(sc, W, H, spp, depth, 77, nthreads=64, rng=RNG_PHILOX | OPT_BOOK, want_fixed=True)
+    assert_bits_equal(acc[..., :3], o["fixed"], "book optics: 32.32 radiance sums")
+    st = be.stats()
+    assert st["segments"] == int(o["stats"][0]) and st["sky"] == int(o["stats"][1])
+
+
+def test_book_optics_changes_what_it_should(be, port):
+    """Property checks: (1) with the camera at the origin, zero aperture and no glass, book optics differs from the
+    reference only by the sky blend; (2) glass stops trapping paths (quirk F5 makes 5-8 % of the huge scene's paths
+    hit the depth cap); (3) the throughput build agrees with the parity build statistically; (4) default renders are
+    untouched by the flag's existence."""
+    W, H = 160, 90
+    sc = scenes.huge_scene(W, H)
+    setup(be, sc, W, H)
+    be.clear(); be.reset_stats()
+    be.render(64, 50, seed=5, flags=0)
+    ref_stats = be.stats(); ref_img = be.readback_f32().copy()
+    be.clear(); be.reset_stats()
+    be.render(64, 50, seed=5, flags=FLAG_BOOK_OPTICS)
+    book_stats = be.stats(); book_img = be.readback_f32().copy()
+    assert ref_stats["capped"] / ref_stats["samples"] > 0.03
+    assert book_stats["capped"] / book_stats["samples"] < 0.2 * ref_stats["capped"] / ref_stats["samples"]
+    # sky: the reference's .5*y + 1.0 extrapolates past pure blue (red channel down to .25); the [0,1] blend stays whiter
+    assert book_img[0, :, 0].mean() > ref_img[0, :, 0].mean() + 0.15 and book_img[0, :, 2].mean() == 1.0
+    be.clear()
+    be.render(64, 50, seed=5, flags=FLAG_BOOK_OPTICS | FLAG_EXACT)
+    exact_img = be.readback_f32().copy()
+    assert abs(float(exact_img.mean()) - float(book_img.mean())) < 0.01
+    blk = lambda im: im.reshape(H // 10, 10, W // 10, 10, 3).mean((1, 3))
+    assert np.abs(blk(exact_img) - blk(book_img)).max() < 0.06
+    # lambert-only scene, pinhole camera at the origin: only the sky term differs -> identical path statistics
+    lam = scenes.Scene("lambert", sc.spheres[:40].copy(), np.zeros(40, np.uint32), np.array([[.5, .5, .5, 0]], np.float32),
+                       np.zeros(1, np.uint32), sc.with_camera(aperture=0.0).camera)
+    setup(be, lam, W, H)
+    out = {}
+    for f in (0, FLAG_BOOK_OPTICS):
+        be.clear(); be.reset_stats(); be.render(8, 50, seed=9, flags=FLAG_EXACT | f)
+        out[f] = be.stats()
+    for k in ("segments", "sky", "capped", "absorbed"):
+        assert out[0][k] == out[FLAG_BOOK_OPTICS][k], k
 
 
 def test_edge_cases_and_errors(be):

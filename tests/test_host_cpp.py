@@ -65,6 +65,25 @@ def test_demo_main_equals_c_abi_render(tmp_path, be):
 
 
 @pytest.mark.gpu
+def test_demo_progressive_passes_give_the_one_shot_image(tmp_path, be):
+    """rtiow_demo --spp-per-pass: the C++ cuda_impl overload drives rt_render_progressive; previews are written as PPMs
+    and the final frame equals the one-shot frame bit for bit."""
+    out = str(tmp_path / "prog.ppm")
+    pre = str(tmp_path / "prev_")
+    res = subprocess.run([DEMO, "--scene", "huge", "--width", "320", "--height", "180", "--spp", "8", "--depth", "50",
+                          "--seed", "5", "--spp-per-pass", "3", "--preview-prefix", pre, "--out", out],
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    assert [l for l in res.stdout.splitlines() if l.startswith("preview:")] == \
+        ["preview: pass 1, 3 spp", "preview: pass 2, 6 spp", "preview: pass 3, 8 spp"]
+    ref = be.render_frame(scenes.huge_scene(320, 180), 320, 180, 8, 50, seed=5)
+    assert_bits_equal(read_ppm(out), ref, "progressive demo frame")
+    assert_bits_equal(read_ppm(pre + "8.ppm"), ref, "last preview")
+    part = be.render_frame(scenes.huge_scene(320, 180), 320, 180, 3, 50, seed=5)
+    assert_bits_equal(read_ppm(pre + "3.ppm"), part, "first preview")
+
+
+@pytest.mark.gpu
 def test_reference_main_runs_on_this_backend(tmp_path, be):
     """The reference's OWN main.cxx, linked against our cuda_impl, writes image_cuda.ppm (src/main.cxx:104-118):
     1920x1080, the reference GPU path's scene at 48 spp / 32 bounces."""
