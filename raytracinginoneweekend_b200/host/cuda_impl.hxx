@@ -23,6 +23,7 @@ struct cuda_impl_options final {
     std::uint32_t max_depth{32};           // src/CUDA/cuda_impl.cu:60
     std::uint64_t seed{1};
     bool exact{false};                     // parity build (no FMA contraction)
+    bool book_optics{false};               // RT_FLAG_BOOK_OPTICS: textbook refraction / camera / sky instead of the reference's
     int device{0};
     // progressive rendering (rt_render_progressive): passes of this many samples (0 = one shot) and, every
     // `preview_every` passes, the image so far handed to `on_preview` while the next pass renders; return true to stop

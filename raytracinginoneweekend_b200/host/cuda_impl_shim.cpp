@@ -65,7 +65,8 @@ void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8ve
     p.max_depth = options.max_depth;
     p.seed = options.seed;
     p.sample_base = 0;
-    p.flags = options.exact ? static_cast<std::uint32_t>(RT_FLAG_EXACT) : 0u;
+    p.flags = (options.exact ? static_cast<std::uint32_t>(RT_FLAG_EXACT) : 0u) |
+              (options.book_optics ? static_cast<std::uint32_t>(RT_FLAG_BOOK_OPTICS) : 0u);
     static_assert(sizeof(math::u8vec3) == 3, "texels are tightly packed RGB8");
     auto *texels = reinterpret_cast<std::uint8_t *>(image_texels.data());
     if (options.samples_per_pass == 0) {

@@ -1,7 +1,7 @@
 // host/main_demo.cxx -- what the reference's main() does (src/main.cxx:104-118: size the output, call
 // cuda_impl, write a P6 PPM), with the scene, size, spp and depth on the command line.
 //   rtiow_demo [--scene simple|huge|synthetic:N] [--width W] [--height H] [--spp S] [--depth D] [--seed X]
-//              [--exact] [--out image.ppm] [--dump-scene file.bin]
+//              [--exact] [--book-optics] [--out image.ppm] [--dump-scene file.bin]
 //              [--spp-per-pass P [--preview-every K] [--preview-prefix path_]]   progressive passes with previews
 #include <cstdint>
 #include <cstdio>
@@ -72,6 +72,7 @@ int main(int argc, char **argv)
             else if (a == "--seed") opt.seed = std::stoull(next());
             else if (a == "--device") opt.device = std::stoi(next());
             else if (a == "--exact") opt.exact = true;
+            else if (a == "--book-optics") opt.book_optics = true;
             else if (a == "--spp-per-pass") opt.samples_per_pass = static_cast<std::uint32_t>(std::stoul(next()));
             else if (a == "--preview-every") opt.preview_every = static_cast<std::uint32_t>(std::stoul(next()));
             else if (a == "--preview-prefix") preview_prefix = next();
