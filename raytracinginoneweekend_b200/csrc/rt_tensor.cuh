@@ -30,7 +30,16 @@
 
 // RT_TC_WGS / RT_TC_CHUNK / RT_TC_NBUF (rt_types.h): ray warpgroups per CTA, spheres per accumulator tile, tiles per warpgroup
 #define RT_TC_RAY_THREADS (RT_TC_WGS * 128)
-#define RT_TC_THREADS (RT_TC_RAY_THREADS + 128)          // + one warpgroup of MMA issuers (one warp per ray warpgroup)
+#define RT_TC_ISSUER_THREADS (((RT_TC_WGS + 3) / 4) * 128)   // whole warpgroups (setmaxnreg is per warpgroup), one issuer warp per ray warpgroup
+#define RT_TC_THREADS (RT_TC_RAY_THREADS + RT_TC_ISSUER_THREADS)
+// register hand-over (the pool is the CTA's own allocation: what the issuers free must cover what the ray warps take)
+//   4 ray warpgroups: 640 threads x 96 at launch; issuers 24, ray warps 112  (128 x 72 freed >= 512 x 16 taken)
+//   5 ray warpgroups: 896 threads x 72 at launch; issuers 24, ray warps 88   (256 x 48 freed >= 640 x 16 taken)
+#if RT_TC_WGS == 4
+#define RT_TC_REG_RAY "112"
+#elif RT_TC_WGS == 5
+#define RT_TC_REG_RAY "88"
+#endif
 // with 4 ray warpgroups: 640 threads x 96 registers at launch; the issuer warpgroup drops to 24, the ray warpgroups take 112
 // (the pool is the CTA's own allocation: 128 x 72 freed >= 4 x 128 x 16 taken)
 #define RT_TC_KQ 8                        // K = 32 tf32 slots = 8 chunks of 16 bytes
@@ -260,7 +269,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     if (warp >= RT_TC_WGS * 4) {
         // ============================================================ MMA issuer: one thread per warpgroup
         const uint32_t w = warp - RT_TC_WGS * 4;
-#if RT_TC_WGS >= 4
+#ifdef RT_TC_REG_RAY
         asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");                        // hand registers to the ray warpgroups
 #endif
         if (w < RT_TC_WGS) {
@@ -291,8 +300,8 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         __syncwarp();
     } else {
         // ============================================================ ray warps: one path per thread
-#if RT_TC_WGS >= 4
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+#ifdef RT_TC_REG_RAY
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 " RT_TC_REG_RAY ";");
 #endif
         const uint32_t wg = warp >> 2;
         const uint32_t lane_off = ((warp & 3u) * 32u) << 16;

@@ -109,7 +109,7 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #define RT_SMALL_SCENE 12u    // throughput build: at or below this many spheres the closest hit tests every sphere directly (no filter)
 #endif
 #ifndef RT_TC_WGS
-#define RT_TC_WGS 4
+#define RT_TC_WGS 5
 #endif
 #ifndef RT_TC_CHUNK
 #define RT_TC_CHUNK 64
