@@ -141,7 +141,7 @@ RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
 {
     RtDeviceScene s{};
     s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
-    s.n = c->n; s.npad = c->npad;
+    s.n = c->n; s.npad = c->npad; s.m = c->m;
     s.filt = c->d_filt; s.nfilt = c->nfilt; s.sigma = c->sigma; s.S = c->S; s.o_limit2 = c->o_limit2;
     s.tc_b = c->d_tcb; s.tc_ns = c->tc_ns; s.tc_gx = c->tc_g[0]; s.tc_gy = c->tc_g[1]; s.tc_gz = c->tc_g[2];
     s.tc_eps = (float)RT_TC_EPS;
@@ -511,7 +511,8 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     // for the shared-memory sphere matrix or the caller asks for the FMA-pipe filter
     // (below RT_TC_MIN_SPHERES one 128-column tile is mostly padding and the FMA-pipe loop is shorter than the handshake)
     const bool tensor = !exact && !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(p->flags & RT_FLAG_FILTER_FMA);
-    size_t smem = tensor ? rt_render_tc_smem_bytes(c->npad, c->tc_ns) : rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
+    bool smem_mats = false;
+    size_t smem = tensor ? rt_render_tc_smem_bytes(c->npad, c->tc_ns, c->m, &smem_mats) : rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
     int ctas = 1;                      // the tensor kernel owns the SM (all 512 TMEM columns): one CTA per SM
     if (!tensor) {
         r = occupancy(c, exact, lbvh, smem, &ctas);
@@ -543,11 +544,14 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.tiles = d_tiles;
     a.TP = (uint32_t)TP;
     a.TPS = (uint32_t)(TP * p->spp);
+    a.mTP = (uint32_t)(0x100000000ull / a.TP); a.mTPS = (uint32_t)(0x100000000ull / a.TPS);
+    a.mW0 = (uint32_t)(0x100000000ull / (tile0.z ? tile0.z : 1u));
     a.spp = p->spp; a.depth = p->max_depth; a.sample_base = p->sample_base;
     a.key0 = (uint32_t)p->seed; a.key1 = (uint32_t)(p->seed >> 32);
     a.stats = c->d_stats;
     a.check = (p->flags & RT_FLAG_FILTER_CHECK) ? 1u : 0u;
     a.book = (p->flags & RT_FLAG_BOOK_OPTICS) ? 1u : 0u;
+    a.smem_mats = smem_mats ? 1u : 0u;
 
     // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic)
     uint32_t per_band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);

@@ -10,9 +10,14 @@ size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh
     return 128 + ((size_t)npad + nfilt) * 16u + (size_t)RT_FCHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
 }
 // tensor-filter kernel: barriers + B matrix (8 x 16 B per column) + sphere records + 32-sphere mask words (one per ray thread)
-size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns)
+// (+ radii, material indices and materials when they still fit in the 227 KB of one CTA)
+size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns, uint32_t m, bool *mats_in_smem)
 {
-    return 512 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * (RT_TC_WGS * 128u) * 4u;
+    size_t b = 512 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * (RT_TC_WGS * 128u) * 4u;
+    const size_t extra = (size_t)m * 16u + (size_t)npad * 8u;
+    const bool fits = b + extra <= RT_TC_SMEM_LIMIT;
+    if (mats_in_smem) *mats_in_smem = fits;
+    return fits ? b + extra : b;
 }
 size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh)
 {

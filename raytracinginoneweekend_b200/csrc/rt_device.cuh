@@ -561,6 +561,16 @@ __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, uint32_t *
     return item;
 }
 
+// x / d for 32-bit x with M = floor(2^32 / d) (d >= 2; host-computed): the estimate is at most one short.
+__device__ __forceinline__ uint32_t div_magic(uint32_t x, uint32_t d, uint32_t M, uint32_t &rem)
+{
+    uint32_t q = __umulhi(x, M);
+    uint32_t r = x - q * d;
+    if (r >= d) { ++q; r -= d; }
+    rem = r;
+    return q;
+}
+
 // ------------------------------------------------------------------ the persistent render kernel
 enum { ST_EMPTY = 0, ST_ACTIVE = 1, ST_DEAD = 2 };
 enum { RM_NONE = 0, RM_UNIFORM = 1, RM_BALL = 2, RM_CAMERA = 3 };
@@ -584,8 +594,12 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
 template <bool LBVH>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
-                                           float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false)
+                                           float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false,
+                                           const float *__restrict__ s_rad = nullptr, const uint32_t *__restrict__ s_meta = nullptr,
+                                           const float4 *__restrict__ s_mat = nullptr)
 {
+    // s_rad / s_meta / s_mat: shared-memory copies of the radii, material indices and materials when the kernel staged
+    // them (two dependent L2 round trips per hit otherwise)
     // hold: this lane's closest-hit query is still running (resumable LBVH traversal); it only takes part in the
     // warp-cooperative work pool and leaves its path untouched
     const RtDeviceScene &sc = A.sc;
@@ -614,9 +628,9 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             want = true;
         } else {
             float4 s = LBVH ? __ldg(sc.sph + best_i) : s_sph[best_i];
-            float rad = __ldg(sc.sph_rad + best_i);
-            uint32_t meta = __ldg(sc.sph_meta + best_i);
-            m = __ldg(sc.mat + (meta & 0x3fffffffu));
+            float rad = s_rad ? s_rad[best_i] : __ldg(sc.sph_rad + best_i);
+            uint32_t meta = s_meta ? s_meta[best_i] : __ldg(sc.sph_meta + best_i);
+            m = s_mat ? s_mat[meta & 0x3fffffffu] : __ldg(sc.mat + (meta & 0x3fffffffu));
             kind = (int)(meta >> 30);
             p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
 #if RT_EXACT
@@ -653,14 +667,15 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             if (item != 0xffffffffu) {
                 // item order: tile-major, then sample, then pixel -- a tile's accumulators (TP * 32 B) stay
                 // cache-resident while all of its samples are traced
-                uint32_t tl = item / A.TPS;
-                uint32_t q = item - tl * A.TPS;
-                uint32_t s_i = q / A.TP;
-                uint32_t r = q - s_i * A.TP;
+                uint32_t q, r, rx;
+                uint32_t tl = (A.TPS > 1u) ? div_magic(item, A.TPS, A.mTPS, q) : (q = 0u, item);
+                uint32_t s_i = (A.TP > 1u) ? div_magic(q, A.TP, A.mTP, r) : (r = 0u, q);
                 uint4 T = A.tiles ? __ldg(A.tiles + A.t0 + tl) : A.tile0;
                 if (r < T.z * T.w) {                                      // edge tiles leave slots unused
-                    uint32_t ty = r / T.z;
-                    px = T.x + (r - ty * T.z);
+                    uint32_t ty;
+                    if (!A.tiles && T.z > 1u) ty = div_magic(r, T.z, A.mW0, rx);
+                    else { ty = r / T.z; rx = r - ty * T.z; }
+                    px = T.x + rx;
                     py = T.y + ty;
                     S.pix = py * A.W + px;
                     S.smp = A.sample_base + s_i;

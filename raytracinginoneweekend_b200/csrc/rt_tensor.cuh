@@ -245,6 +245,15 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     float4 *s_b = reinterpret_cast<float4 *>(smem_raw + 512);
     float4 *s_sph = s_b + (size_t)ns * RT_TC_KQ;
     uint32_t *s_mask = reinterpret_cast<uint32_t *>(s_sph + npad);
+    // radii, material indices and materials next to the spheres when they fit (rt_render_tc_smem_bytes)
+    const bool mats_in_smem = A.smem_mats != 0u;
+    float4 *s_mat = reinterpret_cast<float4 *>(s_mask + (size_t)(ns / 32u) * RT_TC_RAY_THREADS);
+    float *s_rad = reinterpret_cast<float *>(s_mat + A.sc.m);
+    uint32_t *s_meta = reinterpret_cast<uint32_t *>(s_rad + npad);
+    if (mats_in_smem) {
+        for (uint32_t i = threadIdx.x; i < A.sc.m; i += RT_TC_THREADS) s_mat[i] = __ldg(A.sc.mat + i);
+        for (uint32_t i = threadIdx.x; i < n; i += RT_TC_THREADS) { s_rad[i] = __ldg(A.sc.sph_rad + i); s_meta[i] = __ldg(A.sc.sph_meta + i); }
+    }
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
     const uint32_t nch = ns / RT_TC_CHUNK;
 
@@ -322,7 +331,8 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         uint32_t npass = 0;
 #endif
         for (;;) {
-            shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts);
+            shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
+                              mats_in_smem ? s_meta : nullptr, mats_in_smem ? s_mat : nullptr);
             TC_T(0);
             const bool live = (S.st == ST_ACTIVE);
             if (!tc::wg_any(1u + wg, S.st != ST_EMPTY)) {                           // whole warpgroup out of work

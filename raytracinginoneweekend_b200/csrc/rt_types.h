@@ -28,6 +28,7 @@ struct RtDeviceScene {
     const uint32_t *sph_meta;
     const float4 *mat;
     uint32_t n, npad;
+    uint32_t m;                  // materials
     // conservative candidate filter of the throughput build (see rt_device.cuh, closest_hit_brute_fast)
     const float4 *filt;          // float4[nfilt] {cx, cy, cz, S*(r^2 - |c|^2 + eps(|c|^2 + r^2))}; padding has w = -inf
     uint32_t nfilt;              // n rounded up to RT_FGROUP
@@ -68,6 +69,7 @@ struct RtRenderArgs {
     uint32_t t0;                 // first list entry of this launch
     uint32_t TP;                 // pixel slots per tile (nominal tile width * height)
     uint32_t TPS;                // TP * spp: work items per tile
+    uint32_t mTP, mTPS, mW0;     // floor(2^32 / d) for d = TP, TPS, tile0.z: work-item decode without integer division
     uint32_t P;                  // pixel slots of this launch = nt * TP
     uint32_t spp, depth, sample_base;
     uint32_t key0, key1;
@@ -76,6 +78,7 @@ struct RtRenderArgs {
     unsigned long long *stats;   // [0] samples [1] segments [2] sky [3] absorbed [4] capped [5] node_visits [6] sphere tests [7] filter misses
     uint32_t check;              // RT_FLAG_FILTER_CHECK
     uint32_t book;               // RT_FLAG_BOOK_OPTICS
+    uint32_t smem_mats;          // tensor kernel: radii, material indices and materials are staged in shared memory (they fit)
 };
 
 struct RtHitArgs {
@@ -131,6 +134,7 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
 #define RT_TC_MIN_SPHERES 48u
 #define RT_TC_MAX_SPHERES 1024u   // tensor-filter path: B matrix (128 B per sphere) + records + masks fit in shared memory
-size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns);
+size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns, uint32_t m, bool *mats_in_smem);
+#define RT_TC_SMEM_LIMIT 232448u    // 227 KB of dynamic shared memory per CTA on sm_100
 size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);
 size_t rt_hits_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh);
