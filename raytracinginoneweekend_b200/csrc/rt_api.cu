@@ -81,6 +81,7 @@ struct rt_ctx {
     std::vector<EventPair> free_events, pending;
     rt_stats hs{};                          // host-side part of the statistics
     int occ[2][2] = {{0, 0}, {0, 0}};       // cached CTAs/SM [exact][lbvh]
+    int occ_small = 0;                      // cached CTAs/SM of k_render_small
     size_t occ_smem[2][2] = {{0, 0}, {0, 0}};
 };
 
@@ -513,8 +514,13 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     const bool tensor = !exact && !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(p->flags & RT_FLAG_FILTER_FMA);
     bool smem_mats = false;
     size_t smem = tensor ? rt_render_tc_smem_bytes(c->npad, c->tc_ns, c->m, &smem_mats) : rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
+    // throughput build, a handful of spheres: the one-path-per-thread kernel without filter code (k_render_small)
+    const bool small = !exact && !lbvh && c->n <= RT_SMALL_SCENE && !(p->flags & RT_FLAG_FILTER_CHECK);
     int ctas = 1;                      // the tensor kernel owns the SM (all 512 TMEM columns): one CTA per SM
-    if (!tensor) {
+    if (small) {
+        if (c->occ_small == 0) CK(rtf::small_occupancy(&c->occ_small));
+        ctas = c->occ_small > 0 ? c->occ_small : 1;
+    } else if (!tensor) {
         r = occupancy(c, exact, lbvh, smem, &ctas);
         if (r) return r;
     }
@@ -565,12 +571,14 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
             c->counter_slot = 0;
         }
         a.work_counter = c->d_counter + c->counter_slot++;
-        const unsigned long long per_cta = tensor ? (unsigned long long)(RT_TC_WGS * 128) : (unsigned long long)RT_THREADS * RT_RPT;
+        const unsigned long long per_cta = tensor ? (unsigned long long)(RT_TC_WGS * 128)
+                                           : small ? (unsigned long long)RT_THREADS : (unsigned long long)RT_THREADS * RT_RPT;
         unsigned long long want_ctas = (a.total_items + per_cta - 1) / per_cta;
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
-        cudaError_t e = tensor ? rtf::launch_render_tc(a, grid, smem, c->stream)
+        cudaError_t e = small ? rtf::launch_render_small(a, grid, c->stream)
+                        : tensor ? rtf::launch_render_tc(a, grid, smem, c->stream)
                         : exact ? rtx::launch_render(a, grid, smem, c->stream, lbvh)
                                 : rtf::launch_render(a, grid, smem, c->stream, lbvh);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");

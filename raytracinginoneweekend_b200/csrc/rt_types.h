@@ -105,6 +105,8 @@ cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 
 namespace rtf {
 cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_render_small(const RtRenderArgs &a, int grid, cudaStream_t s);
+cudaError_t small_occupancy(int *ctas_per_sm);
 cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, uint32_t key1, int lens, cudaStream_t s);
 }
 // tensor-filter kernel shape (rt_tensor.cuh): RT_TC_WGS ray warpgroups x (32 + RT_TC_NBUF * RT_TC_CHUNK) TMEM columns <= 512
