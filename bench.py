@@ -41,6 +41,7 @@ WORKLOADS = {
     "huge-720p-500spp": ("huge", 1280, 720, 500),
     "huge-4k-1024spp": ("huge", 3840, 2160, 1024),
     "simple-720p-64spp": ("simple", 1280, 720, 64),
+    "synthetic1m-1080p-256spp": ("synthetic1m", 1920, 1080, 256),      # BASELINE configs[4]: GPU-built LBVH
 }
 TILE_W, TILE_H = 128, 64
 
@@ -349,8 +350,36 @@ def run_gpu_arm(args):
                                 "fp32_algorithmic is SURVEY 8(d)'s FP32 model (a fraction above 1 = more sphere tests per second than the FMA pipe could execute)",
                         "fp32_algorithmic": fp32_model, "ms_per_launch": render_ms_per_launch, "rank": 0}
             accel = "brute force: tensor-core candidate filter (sphere matrix in shared memory via TMA, accumulators in TMEM) + reference test on candidates"
+        elif st["node_visits"] > 0:
+            # LBVH: bytes = node visits x 64 B (one node = the boxes of both children) + leaf
+            # tests x 16 B, against the measured HBM copy bandwidth.  The tree's hot levels are L2/L1 resident, so this
+            # is traffic the SMs request, not DRAM traffic (ncu: profiles/r01_ncu_k_render_bvh.json).
+            peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+            hbm = None
+            if os.path.exists(peaks_path):
+                try:
+                    hbm = float(json.load(open(peaks_path)).get("hbm_gbs"))
+                except Exception:
+                    hbm = None
+            peak_src = "MEASURED_PEAKS.json hbm_gbs" if hbm else "fallback 6550 GB/s (B200_PROFILING.md)"
+            hbm = hbm or 6550.0
+            nbytes = (st["node_visits"] * 64.0 + st["sphere_tests"] * 16.0) / max(1, args.steps)
+            ach = nbytes / (render_ms_per_launch * 1e-3) / 1e9
+            try:
+                traffic = json.load(open(prof)).get("k_render_bvh", {}).get("dram_bytes_per_launch") if world == 1 else None
+            except Exception:
+                traffic = None
+            roofline = {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
+                        "kernel": "k_render_bvh (persistent bounce loop, resumable LBVH traversal, stacks in shared memory)",
+                        "peak_source": peak_src,
+                        "byte_model": "node_visits * 64 B + leaf_tests * 16 B (device counters)",
+                        "note": "requested bytes are served mostly by L1/L2 (the capture's DRAM traffic is for 8 spp); the kernel is issue bound (two conservative box tests per node)",
+                        "node_visits_per_segment": st["node_visits"] / max(1, st["segments"]),
+                        "leaf_tests_per_segment": st["sphere_tests"] / max(1, st["segments"]),
+                        "ms_per_launch": render_ms_per_launch, "rank": 0}
+            accel = "GPU-built LBVH (Morton + radix sort + Karras + refit), conservative traversal, reference test at the leaves"
         else:
-            roofline = dict(fp32_model, bound="fp32", traffic=traffic, kernel="k_render (persistent bounce loop: sphere tests + shading)",
+            roofline = dict(fp32_model, bound="fp32", traffic=traffic, kernel="k_render / k_render_small (persistent bounce loop: sphere tests + shading)",
                             ms_per_launch=render_ms_per_launch, rank=0)
             accel = "brute-force (shared-memory SoA spheres)"
         line = {
