@@ -238,6 +238,22 @@ __device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, floa
 // Pass 2: each lane walks its own candidate bits (typically 3-10 of 488 spheres) and runs the exact
 //   reference test.  Lanes skip empty mask words independently, so the warp iterates max-over-lanes
 //   of the candidate COUNT, not the number of mask words.
+// The same test with the root chosen against tmax = FLT_MAX (exactly src/raytracer.hxx:63-89 as hit_world calls it),
+// returned instead of merged: FLT_MAX = no hit.  Merging with `if (t < best_t)` in increasing sphere order gives the
+// result of sphere_candidate_fast (a first root at or beyond best_t makes the second root lose as well), and two such
+// calls are independent, so their latencies overlap.
+__device__ __forceinline__ float sphere_root_fast(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
+                                                  float a, float inv_a)
+{
+    float b;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
+    float sq;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(fmaxf(disc, 0.f)));
+    const float t1 = (-b - sq) * inv_a, t2 = (sq - b) * inv_a;
+    const float t = (t1 > RT_KMIN) ? t1 : t2;
+    return (disc > 0.f && t > RT_KMIN && t < FLT_MAX) ? t : FLT_MAX;
+}
+
 // s_mask layout: [word][ray][thread] (conflict-free).
 template <int R>
 __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_sph, uint32_t n, uint32_t npad,

@@ -329,6 +329,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 #ifdef RT_TC_PROF
         long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
         uint32_t npass = 0;
+        unsigned long long cand_sum = 0, cand_max = 0, live_sum = 0;
 #endif
         for (;;) {
             shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
@@ -423,6 +424,38 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 const float a = ray_a, inv_a = ray_inv_a;
 #if !(RT_TC_INLINE_PASS2 && RT_TC_MASKMODE == 0)
                 uint32_t words = live ? nz : 0u, cand = 0u, w = 0u;
+#ifdef RT_TC_PROF
+                uint32_t my_cands = 0;
+#endif
+#if RT_TC_PASS2_PAIR
+                // two candidates per iteration: the two tests are independent until the merge, so their shared-memory,
+                // FMA and MUFU latencies overlap (2.8 candidates per ray on average, 5.4 for the slowest lane of a warp)
+                auto next = [&]() -> int {
+                    if (cand == 0u) {
+                        if (words == 0u) return -1;
+                        w = (uint32_t)__clz(words);
+                        words &= ~(0x80000000u >> w);
+                        cand = s_mask[w * RT_TC_RAY_THREADS + tid];
+                    }
+                    const int lz = __clz(cand);
+                    cand &= ~(0x80000000u >> lz);
+                    const uint32_t j = (w << 5) + (uint32_t)lz;
+                    return j < n ? (int)j : -1;          // padding columns never test positive; guard anyway
+                };
+                for (;;) {
+                    const int j0 = next();
+                    if (j0 < 0) break;
+                    const int j1 = next();
+                    const float4 s0 = s_sph[j0], s1 = s_sph[j1 < 0 ? j0 : j1];
+                    const float t0 = sphere_root_fast(s0, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a);
+                    const float t1 = sphere_root_fast(s1, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a);
+                    if (t0 < best_t) { best_t = t0; best_i = j0; }
+                    if (j1 >= 0 && t1 < best_t) { best_t = t1; best_i = j1; }
+#ifdef RT_TC_PROF
+                    my_cands += (j1 >= 0) ? 2u : 1u;
+#endif
+                }
+#else
                 for (;;) {
                     if (cand == 0u) {
                         if (words == 0u) break;
@@ -434,7 +467,16 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                     cand &= ~(0x80000000u >> lz);
                     const uint32_t j = (w << 5) + (uint32_t)lz;
                     if (j < n) sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a, best_t, best_i);
+#ifdef RT_TC_PROF
+                    ++my_cands;
+#endif
                 }
+#endif
+#ifdef RT_TC_PROF
+                cand_sum += __reduce_add_sync(RT_FULL, my_cands);
+                cand_max += __reduce_max_sync(RT_FULL, my_cands);
+                live_sum += __popc(__ballot_sync(RT_FULL, live));
+#endif
 #endif
                 if (A.check && live) {              // self-check: the same test over all spheres must agree
                     float ct = FLT_MAX; int ci = -1;
@@ -454,6 +496,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
             printf("warp %2u passes %u | per pass: shade %6.0f  wg-barrier %5.0f  row+st %5.0f  wait-mma %6.0f  ldtm %5.0f  masks %6.0f  pass2 %6.0f\n", warp, npass,
                    (double)prof[0] / npass, (double)prof[1] / npass, (double)prof[2] / npass, (double)prof[3] / npass, (double)prof[4] / npass,
                    (double)prof[5] / npass, (double)prof[6] / npass);
+        if (blockIdx.x == 3 && lane == 0 && (warp & 3u) == 0u)
+            printf("warp %2u candidates per live ray %.2f, warp max per pass %.2f, live lanes %.1f\n", warp,
+                   (double)cand_sum / (double)live_sum, (double)cand_max / npass, (double)live_sum / npass);
 #endif
         uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
 #pragma unroll
