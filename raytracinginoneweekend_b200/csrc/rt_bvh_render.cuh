@@ -20,7 +20,9 @@
 #ifndef RT_BVH_STEPS
 #define RT_BVH_STEPS 2              // node steps between two exit votes
 #endif
-#define RT_BVH_SMEM_DEPTH 40
+#ifndef RT_BVH_SMEM_DEPTH
+#define RT_BVH_SMEM_DEPTH 40       // rt_common.cu sizes the shared-memory stacks for 40 levels; smaller values only for testing the overflow
+#endif
 #define RT_BVH_OVF_DEPTH 64
 
 struct BvhTrav {

@@ -531,6 +531,43 @@ def test_lbvh_render_equals_brute_render(be):
     assert_bits_equal(be.readback_accum(), a, "huge-scene accumulators")
 
 
+def test_lbvh_thin_deep_tree_equals_brute_force(be):
+    """Sphere centres in geometric progression (a long, thin Karras tree) plus a random cloud: the resumable traversal
+    of the render kernel and the one-shot traversal of rt_closest_hits must agree with brute force bit for bit.
+    (Run once with a build that has RT_BVH_SMEM_DEPTH=3, i.e. nearly every push in the local overflow stack: same
+    results -- tools/build_variant.sh ovf -DRT_BVH_SMEM_DEPTH=3; RTIOW_LIB=... pytest -k lbvh.)"""
+    W, H = 64, 36
+    k = np.arange(62, dtype=np.float64)
+    xs = np.concatenate([-(2.0 ** -k), 2.0 ** -k]) * 40.0                 # 124 centres crowding towards x = 0
+    rng = np.random.default_rng(3)
+    sph = np.zeros((len(xs) + 200, 4), np.float32)
+    sph[:len(xs), 0] = xs; sph[:len(xs), 1] = 0.5 * np.sin(np.arange(len(xs))); sph[:len(xs), 2] = -6.0
+    sph[:len(xs), 3] = np.maximum(np.abs(xs) * 0.3, 1e-3)
+    sph[len(xs):, :3] = rng.uniform([-20, -3, -25], [20, 3, -3], size=(200, 3)); sph[len(xs):, 3] = rng.uniform(0.05, 0.6, 200)
+    base = scenes.huge_scene(W, H)
+    m = base.materials.shape[0]
+    sc = scenes.Scene("deep", sph, rng.integers(0, m, len(sph)).astype(np.uint32), base.materials, base.mat_kind,
+                      base.with_camera(aperture=0.0).camera)
+    setup(be, sc, W, H)
+    be.clear(); be.render(6, 50, seed=4, flags=FLAG_EXACT | FLAG_BRUTE)
+    a = be.readback_accum().copy()
+    be.clear(); be.reset_stats(); be.render(6, 50, seed=4, flags=FLAG_EXACT | FLAG_LBVH)
+    assert_bits_equal(be.readback_accum(), a, "deep-tree accumulators")
+    assert be.stats()["node_visits"] > 0
+    rays = bounce_like_rays(sc, 4096, 9)
+    ib, tb, nb = be.closest_hits(rays, flags=FLAG_EXACT | FLAG_BRUTE)
+    il, tl, nl = be.closest_hits(rays, flags=FLAG_EXACT | FLAG_LBVH)
+    assert np.array_equal(ib, il)
+    assert_bits_equal(tb, tl, "t")
+    # throughput build: the LBVH leaf test and the tensor kernel's candidate test round differently, so compare hits
+    ib, tb, nb = be.closest_hits(rays, flags=FLAG_BRUTE)
+    il, tl, nl = be.closest_hits(rays, flags=FLAG_LBVH)
+    assert np.array_equal(ib, il)
+    be.clear(); be.reset_stats(); be.render(6, 50, seed=4, flags=FLAG_LBVH)
+    st = be.stats()
+    assert st["samples"] == W * H * 6 and st["node_visits"] > 0
+
+
 def test_lbvh_million_spheres_builds_and_renders(be):
     """BASELINE config 5 shape: 1M-sphere synthetic scene, GPU-built LBVH, 1920x1080 (1 spp here)."""
     W, H = 1920, 1080
