@@ -312,6 +312,14 @@ def run_gpu_arm(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
+    # per-rank view (diagnosis of stragglers): device time of the timed steps, time inside the render kernels, tiles taken
+    mine = torch.tensor([dev_ms, st["render_ms"], float(sched.own_taken if sched else 0), float(sched.stolen if sched else 0)],
+                        dtype=torch.float64, device=f"cuda:{local}")
+    per_rank = [torch.zeros_like(mine) for _ in range(world)] if world > 1 else [mine]
+    if world > 1:
+        dist.all_gather(per_rank, mine)
+    ranks_info = [{"rank": i, "step_ms": float(v[0]) / max(1, args.steps), "render_kernel_ms": float(v[1]) / max(1, args.steps),
+                   "own_tiles_last_step": int(v[2]), "stolen_tiles_last_step": int(v[3])} for i, v in enumerate(per_rank)]
     dev_ms, e2e_ms, wall_s = (float(x) for x in t.tolist())
     samples, segments, launches = (float(x) for x in work.tolist())
 
@@ -400,6 +408,8 @@ def run_gpu_arm(args):
             "roofline": roofline,
             "wall_s": wall_s,
         }
+        if world > 1:
+            line["ranks"] = ranks_info
         if world == 1 and not args.no_cpu_baseline:
             try:
                 orc = load_cpu_oracle()
