@@ -66,9 +66,11 @@ enum {
                                      src/camera.hxx:46-57), sky blend .5*y + .5 (vs src/main.cxx:71).  Everything else
                                      (closest hit, lambert/metal sampling, Schlick, accumulate, resolve) is unchanged.
                                      rt_render / rt_render_tiles / rt_render_progressive / rt_render_frame only. */
-    /* neither accel flag: brute force up to RT_BRUTE_MAX_SPHERES, LBVH above */
+    /* neither accel flag: parity build -- brute force up to RT_BRUTE_MAX_SPHERES, LBVH above; throughput build -- brute
+       force (tensor-core filter) up to RT_AUTO_LBVH_SPHERES, LBVH above (same image: the LBVH returns the brute-force hit) */
 };
 #define RT_BRUTE_MAX_SPHERES 8192u
+#define RT_AUTO_LBVH_SPHERES 768u
 
 typedef struct rt_ctx rt_ctx;
 

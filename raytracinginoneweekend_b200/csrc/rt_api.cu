@@ -159,7 +159,11 @@ int pick_accel(rt_ctx *c, uint32_t flags, bool *lbvh)
     bool want_bvh = (flags & RT_FLAG_ACCEL_LBVH) != 0;
     bool want_brute = (flags & RT_FLAG_ACCEL_BRUTE) != 0;
     if (want_bvh && want_brute) return fail(RT_ERR_INVALID, "both RT_FLAG_ACCEL_BRUTE and RT_FLAG_ACCEL_LBVH set");
-    if (!want_bvh && !want_brute) want_bvh = c->n > RT_BRUTE_MAX_SPHERES;
+    // automatic choice: the parity build brute-forces whatever fits in shared memory; the throughput build switches
+    // to the LBVH where it overtakes the tensor-filter brute force (measured on synthetic grids, tools/crossover.sh:
+    // 730 spheres 1.96 vs 1.74 Gsamples/s, 1025 spheres 0.64 (FMA filter) vs 2.35)
+    if (!want_bvh && !want_brute)
+        want_bvh = c->n > ((flags & RT_FLAG_EXACT) ? RT_BRUTE_MAX_SPHERES : RT_AUTO_LBVH_SPHERES);
     if (!want_bvh && c->n > RT_BRUTE_MAX_SPHERES)
         return fail(RT_ERR_INVALID, "brute force supports at most RT_BRUTE_MAX_SPHERES spheres (shared-memory staging)");
     if (want_bvh && c->n < 2) return fail(RT_ERR_INVALID, "the LBVH needs at least 2 spheres");
@@ -944,7 +948,8 @@ int rt_filter_info(rt_ctx *c, uint32_t out[4])
 {
     if (!c || !out) return fail(RT_ERR_INVALID, "rt_filter_info: NULL argument");
     // which candidate filter the throughput build runs for the uploaded scene, and the GEMM shape per 128 rays
-    const bool tensor = c->d_tcb && c->n >= RT_TC_MIN_SPHERES;
+    // (default dispatch: above RT_AUTO_LBVH_SPHERES the throughput build takes the LBVH unless RT_FLAG_ACCEL_BRUTE is set)
+    const bool tensor = c->d_tcb && c->n >= RT_TC_MIN_SPHERES && c->n <= RT_AUTO_LBVH_SPHERES;
     out[0] = tensor ? 1u : 0u;
     out[1] = tensor ? c->tc_ns : c->nfilt;      // sphere columns per ray (padded)
     out[2] = tensor ? 32u : 0u;                 // K (tf32 slots)

@@ -275,12 +275,12 @@ def test_tensor_filter_never_drops_a_hit(be, n):
     W, H = 192, 108
     sc = scenes.huge_scene(W, H) if n == 488 else random_scene(n, 1000 + n, W, H)
     setup(be, sc, W, H)
-    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK)
+    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK | FLAG_BRUTE)
     st = be.stats()
-    assert st["segments"] > 2 * W * H
+    assert st["segments"] > 2 * W * H and st["node_visits"] == 0
     assert st["filter_misses"] == 0, f"{st['filter_misses']} of {st['segments']} segments lost their closest hit"
     be.clear(); be.reset_stats()
-    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK | FLAG_FILTER_FMA)
+    be.render(6, 50, seed=11 + n, flags=FLAG_FILTER_CHECK | FLAG_FILTER_FMA | FLAG_BRUTE)
     st = be.stats()
     assert st["filter_misses"] == 0, "FMA-pipe filter dropped a hit"
 
