@@ -111,7 +111,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 }
 // tensor-filter kernel shape (rt_tensor.cuh): RT_TC_WGS ray warpgroups x (32 + RT_TC_NBUF * RT_TC_CHUNK) TMEM columns <= 512
 #ifndef RT_SMALL_SCENE
-#define RT_SMALL_SCENE 12u    // throughput build: at or below this many spheres the closest hit tests every sphere directly (no filter)
+#define RT_SMALL_SCENE 47u    // throughput build: at or below this many spheres the closest hit tests every sphere directly (k_render_small;
+                              // measured against the FMA-filter kernel and the tensor kernel, tools/midsize.sh: 37 spheres 3.63 vs 3.08
+                              // vs 3.31 Gsamples/s, 50 spheres 4.23 vs 4.42 (tensor))
 #endif
 #ifndef RT_TC_PASS2_PAIR
 #define RT_TC_PASS2_PAIR 0      // tensor kernel: 1 = the candidate loop tests two candidates per iteration (measured: 1.805 vs 1.816 Gsamples/s, not kept)
@@ -137,7 +139,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #define RT_TC_NEG -1.f            // accumulators hold -q (sign bit = candidate), columns in sphere order
 #endif
 #define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
+#ifndef RT_TC_MIN_SPHERES
 #define RT_TC_MIN_SPHERES 48u
+#endif
 #define RT_TC_MAX_SPHERES 1024u   // tensor-filter path: B matrix (128 B per sphere) + records + masks fit in shared memory
 size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns, uint32_t m, bool *mats_in_smem);
 #define RT_TC_SMEM_LIMIT 232448u    // 227 KB of dynamic shared memory per CTA on sm_100
