@@ -23,9 +23,10 @@
 // Handshakes are mbarriers only: a_ready (ray rows stored) -> issuer; full[b] (tcgen05.commit) -> ray warps;
 // empty[b] (accumulators copied to registers) -> issuer.  A tile is 64 spheres = 4 MMAs (M128 N64 K8).
 // Measured shapes (huge scene, Gsamples/s): 3 warpgroups x 128 columns 1.33, 3 x (2 x 64) 1.35, 4 x 96 1.43, 4 x 64 1.46,
-// 4 x (3 x 32) 1.18; candidate tests inlined per tile (RT_TC_INLINE_PASS2) 1.42.
-// Epilogue: tcgen05.ld 32 columns -> 32 registers -> sign mask with 16 I2IP (two saturating s32->u8 packs per
-// op) + 8 LOP3 -> the non-empty mask words go to shared memory -> pass 2 as in the FMA-pipe build.
+// 4 x (3 x 32) 1.18; candidate tests inlined per tile (RT_TC_INLINE_PASS2) 1.42; with the inversion sampler 4 x 64 1.64,
+// 5 x 64 (shipped) 1.82, + I2IP.U2 masks 1.85-1.89.
+// Epilogue: tcgen05.ld 2 x 32 columns -> 64 registers -> two sign-mask words (16 I2IP.U2 + 1 LOP3 each, RT_TC_MASKMODE)
+// -> the non-empty mask words go to shared memory -> pass 2 as in the FMA-pipe build.
 #pragma once
 
 // RT_TC_WGS / RT_TC_CHUNK / RT_TC_NBUF (rt_types.h): ray warpgroups per CTA, spheres per accumulator tile, tiles per warpgroup
@@ -138,10 +139,9 @@ __device__ __forceinline__ float tf32_round(float x)
                  : "memory")
 
 // Sign masks of 32 accumulator words -> one 32-bit candidate mask whose __clz order is the sphere order.
-// RT_TC_MASKMODE (rt_types.h) selects the reduction; the host lays the sphere matrix out accordingly:
+// RT_TC_MASKMODE (rt_types.h) selects the reduction (default 4); the host lays the sphere matrix out accordingly:
 //   0  I2IP: 16 two-value saturating s32->u8 packs + 8 LOP3.  bit (8p + j) <=> word 4j + 3 - p is a positive float;
-//      the host places sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2).  Fewest issue slots (24
-//      per word) but I2IP is a slow-rate instruction (~8 cycles per warp instruction per SM sub-partition).
+//      the host places sphere 32 b + k in column 32 b + v with k = 7 + 8 (v & 3) - (v >> 2).  24 instructions per word.
 //   1-3  the ray rows are stored NEGATED, a candidate is a NEGATIVE accumulator, word i -> bit 31 - i, identity layout:
 //      1  FMA pipe: t = sat(-2^100 v) in {0,1}, FP32 Horner chains c = 2c + t (exact: chains stay below 2^16), the
 //         two 16-bit halves read out of the mantissa with the 2^23 trick + one PRMT;
@@ -160,6 +160,20 @@ __device__ __forceinline__ uint32_t sign_mask_i2ip(const uint32_t (&v)[32])
         m |= w & (0x01010101u << j);
     }
     return m;
+}
+//   4  I2IP with 2-bit saturation: a positive s32 packs to 0b11, anything else to 0b00, and the instruction shifts its third
+//      operand left by 4 -- a chain of 8 holds 16 values as bit pairs; two chains merge with ONE LOP3 (odd bits of the
+//      first, even bits of the second): 17 instructions per word instead of 24.  bit 31 - 2k <=> word k, bit 30 - 2k <=>
+//      word 16 + k; the host places sphere 32 b + s in column 32 b + (s even ? s/2 : 16 + (s-1)/2).
+__device__ __forceinline__ uint32_t sign_mask_i2ip2(const uint32_t (&v)[32])
+{
+    uint32_t c0 = 0u, c1 = 0u;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        asm("cvt.pack.sat.u2.s32.b32 %0, %1, %2, %3;" : "=r"(c0) : "r"(v[2 * i]), "r"(v[2 * i + 1]), "r"(c0));
+        asm("cvt.pack.sat.u2.s32.b32 %0, %1, %2, %3;" : "=r"(c1) : "r"(v[16 + 2 * i]), "r"(v[17 + 2 * i]), "r"(c1));
+    }
+    return (c0 & 0xaaaaaaaau) | (c1 & 0x55555555u);
 }
 __device__ __forceinline__ uint32_t sign_mask_alu(const uint32_t (&v)[32])
 {
@@ -189,6 +203,8 @@ __device__ __forceinline__ uint32_t sign_mask(const uint32_t (&v)[32])
 {
 #if RT_TC_MASKMODE == 0
     return sign_mask_i2ip(v);
+#elif RT_TC_MASKMODE == 4
+    return sign_mask_i2ip2(v);
 #elif RT_TC_MASKMODE == 1
     return sign_mask_fma(v);
 #elif RT_TC_MASKMODE == 2
@@ -363,7 +379,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 full_parity ^= 1u << b;
                 tc::fence_after();
                 TC_T(3);
-#if RT_TC_MASKMODE == 0
+#if RT_TC_MASK_POSITIVE
 #pragma unroll
                 for (uint32_t i = 0; i < RT_TC_CHUNK / 32; i += 2) {           // 64 columns (one odd 32 at the end) at a time
                     const bool two = i + 1 < RT_TC_CHUNK / 32, last = i + 2 >= RT_TC_CHUNK / 32;
@@ -422,7 +438,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
             // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
             {
                 const float a = ray_a, inv_a = ray_inv_a;
-#if !(RT_TC_INLINE_PASS2 && RT_TC_MASKMODE == 0)
+#if !(RT_TC_INLINE_PASS2 && RT_TC_MASK_POSITIVE)
                 uint32_t words = live ? nz : 0u, cand = 0u, w = 0u;
 #ifdef RT_TC_PROF
                 uint32_t my_cands = 0;

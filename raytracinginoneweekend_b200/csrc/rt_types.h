@@ -131,9 +131,10 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #define RT_TC_INLINE_PASS2 0       // 1: run the candidate tests of a tile right after its sign masks (overlaps the next tile's MMAs)
 #endif
 #ifndef RT_TC_MASKMODE
-#define RT_TC_MASKMODE 0          // sign-mask reduction of the accumulators (tc::sign_mask): 0 I2IP, 1 FMA pipe, 2 ALU pipe, 3 both
+#define RT_TC_MASKMODE 4          // sign-mask reduction of the accumulators (tc::sign_mask): 0 I2IP.U8, 1 FMA pipe, 2 ALU pipe, 3 both, 4 I2IP.U2
 #endif
-#if RT_TC_MASKMODE == 0
+#define RT_TC_MASK_POSITIVE (RT_TC_MASKMODE == 0 || RT_TC_MASKMODE == 4)
+#if RT_TC_MASK_POSITIVE
 #define RT_TC_NEG 1.f             // accumulators hold +q, columns permuted to the I2IP bit order
 #else
 #define RT_TC_NEG -1.f            // accumulators hold -q (sign bit = candidate), columns in sphere order
