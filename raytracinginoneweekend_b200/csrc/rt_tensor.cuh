@@ -31,12 +31,18 @@
 
 // RT_TC_WGS / RT_TC_CHUNK / RT_TC_NBUF (rt_types.h): ray warpgroups per CTA, spheres per accumulator tile, tiles per warpgroup
 #define RT_TC_RAY_THREADS (RT_TC_WGS * 128)
+#if RT_TC_SELFISSUE
+#define RT_TC_ISSUER_THREADS 0          // the last ray warp to arrive issues the MMAs itself: no issuer warps
+#else
 #define RT_TC_ISSUER_THREADS (((RT_TC_WGS + 3) / 4) * 128)   // whole warpgroups (setmaxnreg is per warpgroup), one issuer warp per ray warpgroup
+#endif
 #define RT_TC_THREADS (RT_TC_RAY_THREADS + RT_TC_ISSUER_THREADS)
 // register hand-over (the pool is the CTA's own allocation: what the issuers free must cover what the ray warps take)
 //   4 ray warpgroups: 640 threads x 96 at launch; issuers 24, ray warps 112  (128 x 72 freed >= 512 x 16 taken)
 //   5 ray warpgroups: 896 threads x 72 at launch; issuers 24, ray warps 88   (256 x 48 freed >= 640 x 16 taken)
-#if RT_TC_WGS == 4
+#if RT_TC_SELFISSUE
+// no hand-over: 640 threads get up to 96 registers each from the launch bound alone
+#elif RT_TC_WGS == 4
 #define RT_TC_REG_RAY "112"
 #elif RT_TC_WGS == 5
 #define RT_TC_REG_RAY "88"
@@ -48,7 +54,10 @@
 #define RT_TC_WGBARS (1 + 2 * RT_TC_NBUF)              // a_ready, full[NBUF], empty[NBUF]
 static_assert(RT_TC_WGS * RT_TC_WGCOLS <= 512, "TMEM has 512 columns");
 static_assert(RT_TC_CHUNK % 32 == 0 && RT_TC_CHUNK >= 32 && RT_TC_CHUNK <= 256, "tile width: whole mask words, one MMA N");
-static_assert((1 + RT_TC_WGS * RT_TC_WGBARS) * 8 <= 448 && 452 + 4 * RT_TC_WGS <= 512, "barriers, TMEM base and done flags live in the first 512 bytes of shared memory");
+static_assert((1 + RT_TC_WGS * RT_TC_WGBARS) * 8 <= 448 && 452 + 12 * RT_TC_WGS <= 512, "barriers, TMEM base, done flags and arrival counters live in the first 512 bytes of shared memory");
+#if RT_TC_SELFISSUE
+static_assert(RT_TC_NBUF == 1 && RT_TC_MASK_POSITIVE && !RT_TC_INLINE_PASS2, "the self-issuing handshake: one accumulator tile per warpgroup, I2IP masks");
+#endif
 
 #ifdef RT_TC_PROF
 #define TC_T(k) do { long long t_ = clock64(); prof[k] += t_ - tprev; tprev = t_; } while (0)
@@ -101,6 +110,17 @@ __device__ __forceinline__ void bar_wait_sleep(uint64_t *bar, uint32_t parity)
         "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, 0x989680;\n"
         "@P1 bra TC_DONES;\nbra TC_WAITS;\nTC_DONES:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// issuer-side wait for the ray rows (a long wait: the ray warps are in pass 2 / shading): back off with nanosleep
+__device__ __forceinline__ void bar_wait_nanosleep(uint64_t *bar, uint32_t parity, uint32_t ns)
+{
+    for (;;) {
+        uint32_t ok;
+        asm volatile("{\n.reg .pred P1;\nmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\nselp.u32 %0, 1, 0, P1;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) break;
+        __nanosleep(ns);
+    }
+}
 __device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // warpgroup-wide OR over a named barrier (ids 1..RT_TC_WGS)
@@ -110,6 +130,33 @@ __device__ __forceinline__ bool wg_any(uint32_t id, bool pred)
     asm volatile("{\n.reg .pred p, q;\nsetp.ne.u32 q, %1, 0;\nbar.red.or.pred p, %2, 128, q;\nselp.u32 %0, 1, 0, p;\n}"
                  : "=r"(r) : "r"((uint32_t)pred), "r"(id) : "memory");
     return r != 0u;
+}
+// Arrival counter of the self-issuing handshake (RT_TC_SELFISSUE): returns the count before this arrival; the
+// arrival whose old value is 3 mod 4 is the last of its warpgroup and issues the next tile's MMAs.  acq_rel at CTA
+// scope orders the other warps' completed tcgen05.st / tcgen05.ld before the issue.
+__device__ __forceinline__ uint32_t cnt_arrive(uint32_t *cnt)
+{
+    uint32_t old;
+#if RT_TC_SELFISSUE == 2
+    asm volatile("atom.relaxed.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(cnt)) : "memory");
+#else
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(cnt)) : "memory");
+#endif
+    return old;
+}
+// The same on an mbarrier with 4 expected arrivals (RT_TC_SELFISSUE == 3): arrive (release) returns the state before the
+// arrival; a pending count of 1 means this was the last one, and a test_wait (acquire) on that phase -- complete by
+// construction -- orders the other warps' work before the issue.  Returns 3 for the last arriver, 0 otherwise.
+__device__ __forceinline__ uint32_t bar_arrive_last(uint64_t *bar)
+{
+    uint32_t last;
+    asm volatile("{\n.reg .b64 st;\n.reg .u32 pc;\n.reg .pred p, q;\n"
+                 "mbarrier.arrive.shared::cta.b64 st, [%1];\n"
+                 "mbarrier.pending_count.b64 pc, st;\n"
+                 "setp.eq.u32 p, pc, 1;\n"
+                 "@p mbarrier.test_wait.shared::cta.b64 q, [%1], st;\n"
+                 "selp.u32 %0, 3, 0, p;\n}" : "=r"(last) : "r"(smem_u32(bar)) : "memory");
+    return last;
 }
 __device__ __forceinline__ float tf32_round(float x)
 {
@@ -257,6 +304,10 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(smem_raw + 448);
     volatile uint32_t *s_done = reinterpret_cast<volatile uint32_t *>(smem_raw + 452);
+#if RT_TC_SELFISSUE || RT_TC_NOVOTE
+    uint32_t *s_cnt = reinterpret_cast<uint32_t *>(smem_raw + 452 + 4 * RT_TC_WGS);                  // arrivals (a_ready / tile consumed)
+    uint32_t *s_fin = reinterpret_cast<uint32_t *>(smem_raw + 452 + 8 * RT_TC_WGS);                  // warps that ran out of work for good
+#endif
     const uint32_t ns = A.sc.tc_ns, npad = A.sc.npad, n = A.sc.n;
     float4 *s_b = reinterpret_cast<float4 *>(smem_raw + 512);
     float4 *s_sph = s_b + (size_t)ns * RT_TC_KQ;
@@ -279,6 +330,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
             tc::bar_init(bw, 4);
             for (int b = 0; b < RT_TC_NBUF; ++b) { tc::bar_init(bw + 1 + b, 1); tc::bar_init(bw + 1 + RT_TC_NBUF + b, 4); }
             s_done[w] = 0u;
+#if RT_TC_SELFISSUE || RT_TC_NOVOTE
+            s_cnt[w] = 0u; s_fin[w] = 0u;
+#endif
         }
     }
     stage_spheres(s_sph, A.sc.sph, s_b, A.sc.tc_b, npad, ns * RT_TC_KQ, bars);      // inits bars[0], fences, TMA, wait
@@ -291,6 +345,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     tc::fence_after();
     const uint32_t tmem_base = *s_tmem;
 
+#if !RT_TC_SELFISSUE
     if (warp >= RT_TC_WGS * 4) {
         // ============================================================ MMA issuer: one thread per warpgroup
         const uint32_t w = warp - RT_TC_WGS * 4;
@@ -304,8 +359,19 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         const uint32_t tmem_a = tmem_base + w * RT_TC_WGCOLS, tmem_d = tmem_a + 32;
         uint32_t uses = 0;                                                          // tiles issued so far
         for (uint32_t pass = 0;; ++pass) {
+#if RT_TC_AREADY_SLEEP
+            tc::bar_wait_nanosleep(bar + 0, pass & 1u, RT_TC_AREADY_SLEEP);
+#else
             tc::bar_wait_sleep(bar + 0, pass & 1u);                                 // ray rows are in TMEM
+#endif
+#if RT_TC_NOVOTE
+            if (*reinterpret_cast<volatile uint32_t *>(s_fin + w) >= 4u) {          // all four warps are out of work for good:
+                if (lane == 0) { s_done[w] = 1u; tc::bar_arrive(bar + 1); }         // wake them (release) without an MMA
+                break;
+            }
+#else
             if (s_done[w]) break;
+#endif
             for (uint32_t c = 0; c < nch; ++c) {
                 const uint32_t b = c % RT_TC_NBUF;                                  // nch is a multiple of NBUF: b = uses % NBUF too
                 if (uses >= RT_TC_NBUF)                                             // previous tile in this buffer consumed
@@ -323,7 +389,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         }
         }
         __syncwarp();
-    } else {
+    } else
+#endif
+    {
         // ============================================================ ray warps: one path per thread
 #ifdef RT_TC_REG_RAY
         asm volatile("setmaxnreg.inc.sync.aligned.u32 " RT_TC_REG_RAY ";");
@@ -333,6 +401,24 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         const uint32_t tmem_a = tmem_base + wg * RT_TC_WGCOLS + lane_off, tmem_d = tmem_a + 32;
         uint64_t *bar = bars + 1 + wg * RT_TC_WGBARS;
         uint32_t full_parity = 0;                   // bit b: parity of the next completion of full[b]
+#if RT_TC_SELFISSUE || RT_TC_NOVOTE
+        bool fin_counted = false;
+#endif
+#if RT_TC_SELFISSUE
+        // the MMA operands of this warpgroup (used by whichever warp arrives last)
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(RT_TC_CHUNK >> 3) << 17) | ((128u >> 4) << 24);
+        const uint64_t bdesc0 = tc::smem_desc(smem_u32(s_b), ns * 16u, 128u);
+        const uint32_t tmem_a0 = tmem_base + wg * RT_TC_WGCOLS, tmem_d0 = tmem_a0 + 32;
+        auto issue_tile = [&](uint32_t c) {          // converged warp; one elected lane issues
+            tc::fence_after();
+#pragma unroll
+            for (uint32_t ks = 0; ks < RT_TC_KQ / 2; ++ks) {
+                uint64_t bd = bdesc0 + (uint64_t)(((ks * 2u * ns + c * RT_TC_CHUNK) * 16u) >> 4);
+                tc::mma_tf32_ts(tmem_d0, tmem_a0 + ks * 8u, bd, idesc, ks > 0u ? 1u : 0u);
+            }
+            tc::mma_commit(bar + 1);
+        };
+#endif
 
         PathSlot S;
         S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
@@ -352,6 +438,54 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                               mats_in_smem ? s_meta : nullptr, mats_in_smem ? s_mat : nullptr);
             TC_T(0);
             const bool live = (S.st == ST_ACTIVE);
+#if RT_TC_SELFISSUE
+            // no warpgroup vote: a warp whose 32 slots are empty has an exhausted pool (final), says so once, and keeps
+            // taking part with idle rows until the last arriver of a pass finds all four warps finished
+            if (!fin_counted && !__any_sync(RT_FULL, S.st != ST_EMPTY)) {
+                fin_counted = true;
+                if (lane == 0) atomicAdd(s_fin + wg, 1u);
+            }
+            TC_T(1);
+            {
+                float row[32];
+                tc::ray_row(A.sc, live, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, row);
+                RT_TC_ST32(tmem_a, row);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc::fence_before();
+                __syncwarp();
+                uint32_t old = 0;
+#if RT_TC_SELFISSUE == 3
+                if (lane == 0) old = tc::bar_arrive_last(bar + 0);
+#else
+                if (lane == 0) old = tc::cnt_arrive(s_cnt + wg);
+#endif
+                old = __shfl_sync(RT_FULL, old, 0);
+                if ((old & 3u) == 3u) {                                             // all four warps' rows are in TMEM
+                    if (*reinterpret_cast<volatile uint32_t *>(s_fin + wg) >= 4u) { // ... and all four are out of work
+                        if (lane == 0) { s_done[wg] = 1u; tc::bar_arrive(bar + 1); }   // wake the others (release) without an MMA
+                    } else issue_tile(0u);
+                }
+            }
+            TC_T(2);
+#elif RT_TC_NOVOTE
+            // no warpgroup vote: a warp whose 32 slots are empty has an exhausted pool (final) and says so once; the issuer
+            // reads the count when all four have arrived and ends the warpgroup through full[0]
+            if (!fin_counted && !__any_sync(RT_FULL, S.st != ST_EMPTY)) {
+                fin_counted = true;
+                if (lane == 0) atomicAdd(s_fin + wg, 1u);
+            }
+            TC_T(1);
+            {
+                float row[32];
+                tc::ray_row(A.sc, live, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, row);
+                RT_TC_ST32(tmem_a, row);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) tc::bar_arrive(bar + 0);
+            }
+            TC_T(2);
+#else
             if (!tc::wg_any(1u + wg, S.st != ST_EMPTY)) {                           // whole warpgroup out of work
                 if ((tid & 127u) == 0u) s_done[wg] = 1u;
                 __syncwarp();
@@ -369,6 +503,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 if (lane == 0) tc::bar_arrive(bar + 0);
             }
             TC_T(2);
+#endif
             uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
             best_t = FLT_MAX; best_i = -1;
             const float ray_a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
@@ -377,6 +512,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 const uint32_t b = c % RT_TC_NBUF;
                 tc::bar_wait(bar + 1 + b, (full_parity >> b) & 1u);
                 full_parity ^= 1u << b;
+#if RT_TC_SELFISSUE || RT_TC_NOVOTE
+                if (c == 0u && s_done[wg]) goto tc_finished;                        // woken by the exit arrival, not by an MMA
+#endif
                 tc::fence_after();
                 TC_T(3);
 #if RT_TC_MASK_POSITIVE
@@ -388,6 +526,22 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                     if (two) RT_TC_LD32(v1, tmem_d + b * RT_TC_CHUNK + i * 32u + 32u);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     TC_T(4);
+#if RT_TC_SELFISSUE
+                    uint32_t old = 0;
+                    if (last && c + 1u < nch) {      // the whole tile is in registers: count this warp in ...
+                        tc::fence_before();
+                        __syncwarp();
+#if RT_TC_SELFISSUE == 3
+                        if (lane == 0) old = tc::bar_arrive_last(bar + 0);
+#else
+                        if (lane == 0) old = tc::cnt_arrive(s_cnt + wg);
+#endif
+                        old = __shfl_sync(RT_FULL, old, 0);
+                        if ((old & 3u) == 3u) issue_tile(c + 1u);    // ... and the last of the four issues the next tile
+                    }
+                    const uint32_t w0 = c * (RT_TC_CHUNK / 32) + i;
+                    const uint32_t m0 = tc::sign_mask<0>(v0);
+#else
                     if (last) {                      // the whole tile is in registers: hand the buffer back
                         tc::fence_before();
                         __syncwarp();
@@ -395,6 +549,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                     }
                     const uint32_t w0 = c * (RT_TC_CHUNK / 32) + i;
                     const uint32_t m0 = tc::sign_mask<0>(v0);
+#endif
 #if RT_TC_INLINE_PASS2
                     // pass 2 right here, while the MMAs of the next tile run: this lane's candidates of these 64 columns
                     unsigned long long mm = (unsigned long long)m0 << 32;
@@ -507,6 +662,9 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 #endif
         }
 
+#if RT_TC_SELFISSUE || RT_TC_NOVOTE
+    tc_finished:;
+#endif
 #ifdef RT_TC_PROF
         if (blockIdx.x == 3 && lane == 0)
             printf("warp %2u passes %u | per pass: shade %6.0f  wg-barrier %5.0f  row+st %5.0f  wait-mma %6.0f  ldtm %5.0f  masks %6.0f  pass2 %6.0f\n", warp, npass,

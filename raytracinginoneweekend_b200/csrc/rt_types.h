@@ -127,6 +127,15 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_TC_NBUF
 #define RT_TC_NBUF 1
 #endif
+#ifndef RT_TC_SELFISSUE
+#define RT_TC_SELFISSUE 0          // 1: no issuer warps -- the last ray warp to arrive (shared-memory arrival counter) issues the tile's MMAs
+#endif
+#ifndef RT_TC_NOVOTE
+#define RT_TC_NOVOTE 0             // 1: no per-pass warpgroup vote (bar.red) -- finished warps are counted and the issuer ends the warpgroup
+#endif
+#ifndef RT_TC_AREADY_SLEEP
+#define RT_TC_AREADY_SLEEP 0       // > 0: the issuer backs off this many ns between polls while it waits for the ray rows
+#endif
 #ifndef RT_TC_INLINE_PASS2
 #define RT_TC_INLINE_PASS2 0       // 1: run the candidate tests of a tile right after its sign masks (overlaps the next tile's MMAs)
 #endif

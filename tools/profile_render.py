@@ -2,10 +2,11 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from raytracinginoneweekend_b200 import scenes
-from raytracinginoneweekend_b200.backend import Backend, FLAG_EXACT
+from raytracinginoneweekend_b200.backend import Backend, FLAG_EXACT, FLAG_FILTER_FMA
 name = sys.argv[1] if len(sys.argv) > 1 else "huge"
 spp = int(sys.argv[2]) if len(sys.argv) > 2 else 16
-flags = FLAG_EXACT if (len(sys.argv) > 3 and sys.argv[3] == "exact") else 0
+mode = sys.argv[3] if len(sys.argv) > 3 else ""
+flags = {"exact": FLAG_EXACT, "fma": FLAG_FILTER_FMA}.get(mode, 0)
 W, H = 1280, 720
 be = Backend(0)
 be.upload_scene(scenes.get_scene(name, W, H)); be.framebuffer(W, H)
