@@ -20,9 +20,6 @@
 #ifndef RT_BVH_STEPS
 #define RT_BVH_STEPS 2              // node steps between two exit votes
 #endif
-#ifndef RT_BVH_SMEM_DEPTH
-#define RT_BVH_SMEM_DEPTH 40       // rt_common.cu sizes the shared-memory stacks for 40 levels; smaller values only for testing the overflow
-#endif
 #define RT_BVH_OVF_DEPTH 64
 
 struct BvhTrav {
@@ -77,11 +74,17 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
                 if (!T.active) continue;
                 const float4 *np = sc.bvh_nodes + 4 * (size_t)T.node;
                 const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+#if RT_BVH_CENTER
+                const float4 n3 = __ldg(np + 3);
+                const uint2 ch = make_uint2(__float_as_uint(n3.x), __float_as_uint(n3.y));
+#else
+                const float4 n3 = make_float4(0.f, 0.f, 0.f, 0.f);
                 const uint2 ch = __ldg(reinterpret_cast<const uint2 *>(np + 3));
+#endif
                 ++ts.bvh.nodes;
                 float tl, tr;
-                bool hl = bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tl);
-                bool hr = bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tr);
+                bool hl = RT_BVH_BOX_L(n0, n1, n2, n3, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tl);
+                bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tr);
                 const bool ll = hl && (ch.x >> 31), lr = hr && (ch.y >> 31);
                 if (ll || lr) {                                   // one divergent region for both leaf children
                     if (ll) bvh_leaf(sc, ch.x, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);

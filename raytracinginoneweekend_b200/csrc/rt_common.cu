@@ -5,7 +5,7 @@
 // shared memory of the brute-force kernels: mbarrier + sphere records (+ filter records) + candidate masks
 size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh)
 {
-    if (lbvh) return (size_t)40 * RT_THREADS * 4u;      // traversal stacks of k_render_bvh: [RT_BVH_SMEM_DEPTH][RT_THREADS]
+    if (lbvh) return (size_t)RT_BVH_SMEM_DEPTH * RT_THREADS * 4u;      // traversal stacks of k_render_bvh: [RT_BVH_SMEM_DEPTH][RT_THREADS]
     if (exact) return 128 + (size_t)npad * 16u + (size_t)RT_CHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
     return 128 + ((size_t)npad + nfilt) * 16u + (size_t)RT_FCHUNK_WORDS * RT_RPT * RT_THREADS * 4u;
 }

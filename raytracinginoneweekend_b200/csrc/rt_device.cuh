@@ -480,6 +480,13 @@ __device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, 
     float4 s = __ldg(sc.bvh_leaf_sph + pos);
     int j = (int)__ldg(sc.bvh_prims + pos);
     ++cnt.leaves;
+#if RT_BVH_FASTLEAF && !RT_EXACT
+    {   // the candidate test of the brute-force throughput kernels (reciprocal of a, approximate sqrt) + the (t, index) order
+        const float t = sphere_root_fast(s, ox, oy, oz, dx, dy, dz, a, __frcp_rn(a));
+        if (t < best_t || (t == best_t && t < FLT_MAX && j < best_i)) { best_t = t; best_i = j; }
+        return;
+    }
+#endif
     float b;
     float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
     if (disc > 0.f) {
@@ -511,6 +518,35 @@ __device__ __forceinline__ bool bvh_box(float lox, float loy, float loz, float h
     return tn - fabsf(tn) * 1e-5f <= tf + fabsf(tf) * 1e-5f && tf * 1.00001f >= RT_KMIN && tn - fabsf(tn) * 1e-5f <= best_t;
 }
 
+// The same conservative test on a box stored as centre c, half extent h and hsum = hx + hy + hz (RT_BVH_CENTER):
+// the farthest corner is at L1 distance |c - o|_1 + hsum, and the slab interval of an axis is d i -+ |(h + pad) i| with
+// d = c - o, i = 1 / direction.  A ray parallel to an axis (i = +-inf) makes that axis' bounds NaN or +-inf; fminf / fmaxf
+// drop a NaN, i.e. the axis is ignored -- a superset of the exact answer, which is all a conservative test needs.
+__device__ __forceinline__ bool bvh_box_c(float cx, float cy, float cz, float hx, float hy, float hz, float hsum,
+                                          float ox, float oy, float oz, float ix, float iy, float iz,
+                                          float pad0, float best_t, float &tnear)
+{
+    const float dx = cx - ox, dy = cy - oy, dz = cz - oz;
+    const float far = (fabsf(dx) + fabsf(dy)) + (fabsf(dz) + hsum);
+    const float pad = fmaf(far, 9.765625e-4f, pad0);
+    const float mx = dx * ix, px = (hx + pad) * ix;
+    const float my = dy * iy, py = (hy + pad) * iy;
+    const float mz = dz * iz, pz = (hz + pad) * iz;
+    float tn = mx - fabsf(px), tf = mx + fabsf(px);
+    tn = fmaxf(tn, my - fabsf(py)); tf = fminf(tf, my + fabsf(py));
+    tn = fmaxf(tn, mz - fabsf(pz)); tf = fminf(tf, mz + fabsf(pz));
+    tnear = tn;
+    return tn - fabsf(tn) * 1e-5f <= tf + fabsf(tf) * 1e-5f && tf * 1.00001f >= RT_KMIN && tn - fabsf(tn) * 1e-5f <= best_t;
+}
+// both child boxes of a node (n0..n2 = the first three float4 of the node, hs = the two L1 half extents in centre form)
+#if RT_BVH_CENTER
+#define RT_BVH_BOX_L(n0, n1, n2, n3, ...) bvh_box_c(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n3.z, __VA_ARGS__)
+#define RT_BVH_BOX_R(n0, n1, n2, n3, ...) bvh_box_c(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, n3.w, __VA_ARGS__)
+#else
+#define RT_BVH_BOX_L(n0, n1, n2, n3, ...) bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, __VA_ARGS__)
+#define RT_BVH_BOX_R(n0, n1, n2, n3, ...) bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, __VA_ARGS__)
+#endif
+
 __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool live, float ox, float oy, float oz,
                                                  float dx, float dy, float dz, float &best_t, int &best_i, BvhCounters &cnt)
 {
@@ -528,8 +564,8 @@ __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool l
         ++cnt.nodes;
         uint32_t left = __float_as_uint(n3.x), right = __float_as_uint(n3.y);
         float tl, tr;
-        bool hl = bvh_box(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tl);
-        bool hr = bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tr);
+        bool hl = RT_BVH_BOX_L(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tl);
+        bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tr);
         if (hl && (left & 0x80000000u)) { bvh_leaf(sc, left, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hl = false; }
         if (hr && (right & 0x80000000u)) { bvh_leaf(sc, right, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hr = false; }
         if (hl && hr) {                                       // both inner: near child first, far child on the stack

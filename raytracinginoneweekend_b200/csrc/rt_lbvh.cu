@@ -156,6 +156,34 @@ __global__ void k_bvh_refit(const float4 *__restrict__ sph, const float *__restr
     }
 }
 
+#if RT_BVH_CENTER
+// Child boxes (lo, hi) -> (centre, half extent), in place, plus the L1 half extent hx + hy + hz in the two spare words.
+// The half extents are rounded outwards so that [c - h, c + h] contains [lo, hi] in float arithmetic.
+__global__ void k_bvh_center_form(float4 *nodes, uint32_t ninner)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ninner) return;
+    float *f = reinterpret_cast<float *>(nodes + 4 * (size_t)i);
+    float v[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) v[k] = f[k];
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+        float hs = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float lo = v[6 * ch + k], hi = v[6 * ch + 3 + k];
+            const float c = 0.5f * lo + 0.5f * hi;
+            float h = fmaxf(hi - c, c - lo);
+            h = fmaf(fabsf(h) + fabsf(c), 2.4e-7f, h);          // two ulps of the larger magnitude: covers the rounding of c and of h
+            f[6 * ch + k] = c; f[6 * ch + 3 + k] = h;
+            hs += h;
+        }
+        f[14 + ch] = hs * 1.000001f;
+    }
+}
+#endif
+
 template <typename T>
 cudaError_t grow(T **p, size_t count)
 {
@@ -222,6 +250,9 @@ cudaError_t rt_lbvh_build(rt_lbvh *b, const float4 *sph, const float *rad, uint3
     LB(cub::DeviceRadixSort::SortPairs(b->cub_tmp, bytes, b->keys_alt, b->keys, b->vals_alt, b->prims, (int)n, 0, 63, s));
     k_bvh_hierarchy<<<blocks, 256, 0, s>>>(b->keys, (int)n, b->nodes, b->parent);
     k_bvh_refit<<<blocks, 256, 0, s>>>(sph, rad, b->prims, n, b->nodes, b->leaf_sph, b->parent, b->flags);
+#if RT_BVH_CENTER
+    k_bvh_center_form<<<(n - 1u + 255u) / 256u, 256, 0, s>>>(b->nodes, n - 1u);
+#endif
     LB(cudaGetLastError());
     LB(cudaEventRecord(e1, s));
     LB(cudaEventSynchronize(e1));

@@ -115,6 +115,16 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
                               // measured against the FMA-filter kernel and the tensor kernel, tools/midsize.sh: 37 spheres 3.63 vs 3.08
                               // vs 3.31 Gsamples/s, 50 spheres 4.23 vs 4.42 (tensor))
 #endif
+#ifndef RT_BVH_SMEM_DEPTH
+#define RT_BVH_SMEM_DEPTH 40       // levels of the LBVH traversal stack kept in shared memory (k_render_bvh; rt_common.cu sizes it); deeper levels
+                                   // go to a local-memory overflow, so smaller values only change speed (and test the overflow)
+#endif
+#ifndef RT_BVH_CENTER
+#define RT_BVH_CENTER 1     // 1: LBVH nodes hold child boxes as centre + half extent (+ L1 half extent): the padded slab test needs 34 instead of 42 FP32 instructions
+#endif
+#ifndef RT_BVH_FASTLEAF
+#define RT_BVH_FASTLEAF 1   // 1: throughput build: LBVH leaves run the reciprocal / approximate-sqrt candidate test of the brute-force kernels
+#endif
 #ifndef RT_TC_PASS2_PAIR
 #define RT_TC_PASS2_PAIR 0      // tensor kernel: 1 = the candidate loop tests two candidates per iteration (measured: 1.805 vs 1.816 Gsamples/s, not kept)
 #endif
