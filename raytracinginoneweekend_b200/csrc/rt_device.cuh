@@ -478,15 +478,21 @@ __device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, 
 {
     uint32_t pos = ref & 0x7fffffffu;
     float4 s = __ldg(sc.bvh_leaf_sph + pos);
-    int j = (int)__ldg(sc.bvh_prims + pos);
     ++cnt.leaves;
 #if RT_BVH_FASTLEAF && !RT_EXACT
-    {   // the candidate test of the brute-force throughput kernels (reciprocal of a, approximate sqrt) + the (t, index) order
-        const float t = sphere_root_fast(s, ox, oy, oz, dx, dy, dz, a, __frcp_rn(a));
-        if (t < best_t || (t == best_t && t < FLT_MAX && j < best_i)) { best_t = t; best_i = j; }
+    {   // the candidate test of the brute-force throughput kernels (reciprocal of a, approximate sqrt) + the (t, index) order;
+        // the original sphere index is only fetched when the root can still win
+        float inv_a;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_a) : "f"(a));
+        const float t = sphere_root_fast(s, ox, oy, oz, dx, dy, dz, a, inv_a);
+        if (t <= best_t && t < FLT_MAX) {
+            const int j = (int)__ldg(sc.bvh_prims + pos);
+            if (t < best_t || j < best_i) { best_t = t; best_i = j; }
+        }
         return;
     }
 #endif
+    int j = (int)__ldg(sc.bvh_prims + pos);
     float b;
     float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
     if (disc > 0.f) {
