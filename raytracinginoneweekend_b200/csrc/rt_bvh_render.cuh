@@ -93,8 +93,8 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
                 bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, S.ox, S.oy, S.oz, T.ix, T.iy, T.iz, sc.bvh_pad0, T.best_t, tr);
                 const bool ll = hl && (ch.x >> 31), lr = hr && (ch.y >> 31);
                 if (ll || lr) {                                   // one divergent region for both leaf children
-                    if (ll) bvh_leaf(sc, ch.x, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
-                    if (lr) bvh_leaf(sc, ch.y, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
+                    if (ll) RT_BVH_LEAF_L(n0, n1, n2, ch.x, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
+                    if (lr) RT_BVH_LEAF_R(n0, n1, n2, ch.y, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, T.a, T.best_t, T.best_i, ts.bvh);
                 }
                 hl = hl && !(ch.x >> 31); hr = hr && !(ch.y >> 31);
 #if RT_BVH_BRANCHFREE

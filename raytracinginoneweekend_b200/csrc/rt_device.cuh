@@ -473,11 +473,10 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
 //     relative slack.  Culling uses tnear <= best_t (not <), so equal-t candidates with a lower index survive.
 struct BvhCounters { uint32_t nodes, leaves; };
 
-__device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, float ox, float oy, float oz,
-                                         float dx, float dy, float dz, float a, float &best_t, int &best_i, BvhCounters &cnt)
+// Leaf test on a sphere record s = {centre, r*r} at sorted position pos.
+__device__ __forceinline__ void bvh_leaf_sphere(const RtDeviceScene &sc, uint32_t pos, float4 s, float ox, float oy, float oz,
+                                                float dx, float dy, float dz, float a, float &best_t, int &best_i, BvhCounters &cnt)
 {
-    uint32_t pos = ref & 0x7fffffffu;
-    float4 s = __ldg(sc.bvh_leaf_sph + pos);
     ++cnt.leaves;
 #if RT_BVH_FASTLEAF && !RT_EXACT
     {   // the candidate test of the brute-force throughput kernels (reciprocal of a, approximate sqrt) + the (t, index) order;
@@ -503,6 +502,21 @@ __device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, 
         if (ok && (t < best_t || (t == best_t && j < best_i))) { best_t = t; best_i = j; }
     }
 }
+// leaf child `ref` of a node: the sphere comes from the sorted leaf array, or -- RT_BVH_LEAFINNODE -- from the node itself
+// (the child slot of a leaf holds the sphere's centre and |r| in place of a box: no second memory round trip)
+__device__ __forceinline__ void bvh_leaf(const RtDeviceScene &sc, uint32_t ref, float ncx, float ncy, float ncz, float nr,
+                                         float ox, float oy, float oz, float dx, float dy, float dz, float a,
+                                         float &best_t, int &best_i, BvhCounters &cnt)
+{
+    const uint32_t pos = ref & 0x7fffffffu;
+#if RT_BVH_LEAFINNODE
+    bvh_leaf_sphere(sc, pos, make_float4(ncx, ncy, ncz, nr * nr), ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt);
+#else
+    bvh_leaf_sphere(sc, pos, __ldg(sc.bvh_leaf_sph + pos), ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt);
+#endif
+}
+#define RT_BVH_LEAF_L(n0, n1, n2, ref, ...) bvh_leaf(sc, ref, n0.x, n0.y, n0.z, n0.w, __VA_ARGS__)
+#define RT_BVH_LEAF_R(n0, n1, n2, ref, ...) bvh_leaf(sc, ref, n1.z, n1.w, n2.x, n2.y, __VA_ARGS__)
 
 __device__ __forceinline__ bool bvh_box(float lox, float loy, float loz, float hix, float hiy, float hiz,
                                         float ox, float oy, float oz, float ix, float iy, float iz,
@@ -572,8 +586,8 @@ __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool l
         float tl, tr;
         bool hl = RT_BVH_BOX_L(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tl);
         bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, best_t, tr);
-        if (hl && (left & 0x80000000u)) { bvh_leaf(sc, left, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hl = false; }
-        if (hr && (right & 0x80000000u)) { bvh_leaf(sc, right, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hr = false; }
+        if (hl && (left & 0x80000000u)) { RT_BVH_LEAF_L(n0, n1, n2, left, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hl = false; }
+        if (hr && (right & 0x80000000u)) { RT_BVH_LEAF_R(n0, n1, n2, right, ox, oy, oz, dx, dy, dz, a, best_t, best_i, cnt); hr = false; }
         if (hl && hr) {                                       // both inner: near child first, far child on the stack
             bool left_first = tl <= tr;
             stack[sp++] = left_first ? right : left;

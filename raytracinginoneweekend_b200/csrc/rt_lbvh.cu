@@ -159,7 +159,8 @@ __global__ void k_bvh_refit(const float4 *__restrict__ sph, const float *__restr
 #if RT_BVH_CENTER
 // Child boxes (lo, hi) -> (centre, half extent), in place, plus the L1 half extent hx + hy + hz in the two spare words.
 // The half extents are rounded outwards so that [c - h, c + h] contains [lo, hi] in float arithmetic.
-__global__ void k_bvh_center_form(float4 *nodes, uint32_t ninner)
+__global__ void k_bvh_center_form(float4 *nodes, uint32_t ninner, const float4 *__restrict__ leaf_sph,
+                                  const float *__restrict__ rad, const uint32_t *__restrict__ prims)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ninner) return;
@@ -170,6 +171,20 @@ __global__ void k_bvh_center_form(float4 *nodes, uint32_t ninner)
 #pragma unroll
     for (int ch = 0; ch < 2; ++ch) {
         float hs = 0.f;
+#if RT_BVH_LEAFINNODE
+        const uint32_t ref = __float_as_uint(f[12 + ch]);
+        if (ref & 0x80000000u) {
+            // a leaf: the sphere itself.  Centre and |r| exact -- the box [c - |r|, c + |r|] holds the sphere without any rounding,
+            // and |r| * |r| reproduces the record's r*r bit for bit (the leaf test squares it)
+            const uint32_t pos = ref & 0x7fffffffu;
+            const float4 sp = leaf_sph[pos];
+            const float r = fabsf(rad[prims[pos]]);
+            f[6 * ch + 0] = sp.x; f[6 * ch + 1] = sp.y; f[6 * ch + 2] = sp.z;
+            f[6 * ch + 3] = r; f[6 * ch + 4] = r; f[6 * ch + 5] = r;
+            f[14 + ch] = 3.f * r * 1.000001f;
+            continue;
+        }
+#endif
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             const float lo = v[6 * ch + k], hi = v[6 * ch + 3 + k];
@@ -251,7 +266,7 @@ cudaError_t rt_lbvh_build(rt_lbvh *b, const float4 *sph, const float *rad, uint3
     k_bvh_hierarchy<<<blocks, 256, 0, s>>>(b->keys, (int)n, b->nodes, b->parent);
     k_bvh_refit<<<blocks, 256, 0, s>>>(sph, rad, b->prims, n, b->nodes, b->leaf_sph, b->parent, b->flags);
 #if RT_BVH_CENTER
-    k_bvh_center_form<<<(n - 1u + 255u) / 256u, 256, 0, s>>>(b->nodes, n - 1u);
+    k_bvh_center_form<<<(n - 1u + 255u) / 256u, 256, 0, s>>>(b->nodes, n - 1u, b->leaf_sph, rad, b->prims);
 #endif
     LB(cudaGetLastError());
     LB(cudaEventRecord(e1, s));

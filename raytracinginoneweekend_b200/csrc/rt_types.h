@@ -122,6 +122,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_BVH_CENTER
 #define RT_BVH_CENTER 1     // 1: LBVH nodes hold child boxes as centre + half extent (+ L1 half extent): the padded slab test needs 34 instead of 42 FP32 instructions
 #endif
+#ifndef RT_BVH_LEAFINNODE
+#define RT_BVH_LEAFINNODE 1 // 1 (needs RT_BVH_CENTER): the child slot of a leaf holds the sphere (centre, |r|) instead of its box; the leaf test reads no memory
+#endif
 #ifndef RT_BVH_FASTLEAF
 #define RT_BVH_FASTLEAF 1   // 1: throughput build: LBVH leaves run the reciprocal / approximate-sqrt candidate test of the brute-force kernels
 #endif
