@@ -67,7 +67,11 @@ enum {
                                      (closest hit, lambert/metal sampling, Schlick, accumulate, resolve) is unchanged.
                                      rt_render / rt_render_tiles / rt_render_progressive / rt_render_frame only. */
     /* neither accel flag: parity build -- brute force up to RT_BRUTE_MAX_SPHERES, LBVH above; throughput build -- brute
-       force (tensor-core filter) up to RT_AUTO_LBVH_SPHERES, LBVH above (same image: the LBVH returns the brute-force hit) */
+       force (tensor-core filter) up to RT_AUTO_LBVH_SPHERES, LBVH above (same image: the LBVH returns the brute-force hit) */,
+    RT_FLAG_OVERLAP = 1u << 6     /* rt_render_tiles only: this launch may run BESIDE the rt_render_tiles launches queued before it
+                                     (they alternate between two internal streams, so the tail of one persistent launch is
+                                     filled by the next).  The caller promises disjoint tiles within a frame, as the multi-GPU
+                                     tile scheduler does; every other call on the context is ordered after all of them. */
 };
 #define RT_BRUTE_MAX_SPHERES 8192u
 #define RT_AUTO_LBVH_SPHERES 768u

@@ -19,6 +19,7 @@ FLAG_BRUTE = 1 << 1
 FLAG_LBVH = 1 << 2
 FLAG_FILTER_CHECK = 1 << 4  # count segments whose filtered closest hit differs from the unfiltered one (stats: filter_misses)
 FLAG_BOOK_OPTICS = 1 << 5   # opt-in textbook optics (Snell refraction, eye-relative camera rays, disk lens, [0,1] sky blend)
+FLAG_OVERLAP = 1 << 6       # rt_render_tiles: this chunk may run beside the chunks queued before it (disjoint tiles; two internal streams)
 FLAG_FILTER_FMA = 1 << 3   # throughput build: candidate filter on the FMA pipe instead of the tensor cores
 
 EXPORTS = [

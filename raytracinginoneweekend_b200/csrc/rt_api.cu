@@ -47,6 +47,8 @@ struct EventPair { cudaEvent_t a, b; };
 
 }  // namespace
 
+constexpr int kAux = 2;    // auxiliary streams for RT_FLAG_OVERLAP chunks (as many chunks can run beside each other)
+
 struct rt_ctx {
     int device = 0;
     int sm_count = 0;
@@ -73,10 +75,19 @@ struct rt_ctx {
 
     uint32_t *d_counter = nullptr;          // ring of work counters, one per launch
     uint32_t counter_slot = 0;
+    uint4 *d_tile_ring = nullptr;           // ring of tile lists, one slice per launch (no stream-ordered allocation per launch: a block
+    uint32_t tile_ring_pos = 0;             // freed on one stream and reused on another would chain the overlapped launches together)
     unsigned long long *d_stats = nullptr;  // 8 x u64
     float *d_scratch = nullptr;
 
     void *h_pin = nullptr; size_t h_pin_bytes = 0;   // pinned staging for uploads / readbacks
+
+    // RT_FLAG_OVERLAP: chunk launches rotate over kAux auxiliary streams so that the tail of one persistent launch is
+    // filled by the next; aux_tail[i] marks the end of the work queued on aux[i], aux_dirty[i] = c->stream has not waited for it
+    cudaStream_t aux[kAux] = {};
+    cudaEvent_t aux_tail[kAux] = {}, aux_head = nullptr;
+    bool aux_dirty[kAux] = {};
+    int aux_next = 0;
 
     std::vector<EventPair> free_events, pending;
     rt_stats hs{};                          // host-side part of the statistics
@@ -88,6 +99,42 @@ struct rt_ctx {
 namespace {
 
 const uint32_t kCounterRing = 4096;
+const uint32_t kTileRing = 1u << 16;       // tiles (1 MiB)
+
+// Every entry point that queues work on c->stream (or waits for it) goes through here: selects the device and makes
+// c->stream wait for the overlapped chunk launches still running on the auxiliary streams (RT_FLAG_OVERLAP), so that
+// clear / resolve / readback / upload are ordered after them without the caller doing anything.
+cudaError_t enter_ctx(rt_ctx *c)
+{
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return e;
+    for (int i = 0; i < kAux; ++i)
+        if (c->aux_dirty[i]) {
+            e = cudaStreamWaitEvent(c->stream, c->aux_tail[i], 0);
+            if (e != cudaSuccess) return e;
+            c->aux_dirty[i] = false;
+        }
+    return cudaSuccess;
+}
+// stream for the next overlapped launch: ordered after everything queued on c->stream so far, not after the other aux stream
+cudaError_t overlap_stream(rt_ctx *c, cudaStream_t *out, int *slot)
+{
+    cudaError_t e;
+    if (!c->aux[0]) {
+        for (int i = 0; i < kAux; ++i) {
+            if ((e = cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking)) != cudaSuccess) return e;
+            if ((e = cudaEventCreateWithFlags(&c->aux_tail[i], cudaEventDisableTiming)) != cudaSuccess) return e;
+        }
+        if ((e = cudaEventCreateWithFlags(&c->aux_head, cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    const int i = c->aux_next;
+    c->aux_next = (i + 1) % kAux;
+    if ((e = cudaEventRecord(c->aux_head, c->stream)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(c->aux[i], c->aux_head, 0)) != cudaSuccess) return e;
+    *out = c->aux[i];
+    *slot = i;
+    return cudaSuccess;
+}
 
 int ensure_pinned(rt_ctx *c, size_t bytes)
 {
@@ -224,6 +271,7 @@ int rt_create(rt_ctx **out, int device)
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
     CK(cudaMalloc(&c->d_counter, kCounterRing * sizeof(uint32_t)));
+    CK(cudaMalloc(&c->d_tile_ring, (size_t)kTileRing * sizeof(uint4)));
     CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
     CK(cudaMalloc(&c->d_stats, 8 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c->d_stats, 0, 8 * sizeof(unsigned long long), c->stream));
@@ -236,11 +284,17 @@ int rt_destroy(rt_ctx *c)
 {
     if (!c) return RT_OK;
     cudaSetDevice(c->device);
+    for (int i = 0; i < kAux; ++i) if (c->aux[i]) cudaStreamSynchronize(c->aux[i]);
     cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < kAux; ++i) {
+        if (c->aux[i]) cudaStreamDestroy(c->aux[i]);
+        if (c->aux_tail[i]) cudaEventDestroy(c->aux_tail[i]);
+    }
+    if (c->aux_head) cudaEventDestroy(c->aux_head);
     free_scene(c);
     free_framebuffer(c);
     if (c->bvh) rt_lbvh_destroy(c->bvh);
-    cudaFree(c->d_counter); cudaFree(c->d_stats); cudaFree(c->d_scratch);
+    cudaFree(c->d_counter); cudaFree(c->d_tile_ring); cudaFree(c->d_stats); cudaFree(c->d_scratch);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto &p : c->free_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
@@ -252,7 +306,7 @@ int rt_destroy(rt_ctx *c)
 int rt_set_stream(rt_ctx *c, void *cuda_stream)
 {
     if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     CK(cudaStreamSynchronize(c->stream));
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return RT_OK;
@@ -261,7 +315,7 @@ int rt_set_stream(rt_ctx *c, void *cuda_stream)
 int rt_sync(rt_ctx *c)
 {
     if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     CK(cudaStreamSynchronize(c->stream));
     return drain_events(c);
 }
@@ -269,8 +323,8 @@ int rt_sync(rt_ctx *c)
 int rt_throttle(rt_ctx *c, uint32_t max_in_flight)
 {
     if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
-    CK(cudaSetDevice(c->device));
-    // render calls complete in submission order (one stream): retire the oldest until few enough remain
+    CK(cudaSetDevice(c->device));      // a host-side wait only: no join, or the next overlapped chunk would queue behind this one
+    // render calls are retired in submission order (overlapped chunks may finish out of order; waiting for the oldest is enough)
     while (c->pending.size() > max_in_flight) {
         EventPair p = c->pending.front();
         CK(cudaEventSynchronize(p.b));
@@ -288,7 +342,7 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
 {
     if (!c || !spheres || !materials || n == 0 || m == 0) return fail(RT_ERR_INVALID, "rt_scene_upload: empty scene or NULL argument");
     if (m >= (1u << 30)) return fail(RT_ERR_INVALID, "rt_scene_upload: too many materials");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     for (uint32_t i = 0; i < m; ++i)
         if (materials[i].kind > 2u) return fail(RT_ERR_INVALID, "rt_scene_upload: unknown material kind");
     for (uint32_t i = 0; i < n; ++i)
@@ -469,7 +523,7 @@ int rt_framebuffer(rt_ctx *c, uint32_t width, uint32_t height)
 {
     if (!c || width == 0 || height == 0) return fail(RT_ERR_INVALID, "rt_framebuffer: zero size");
     if ((unsigned long long)width * height >= (1ull << 31)) return fail(RT_ERR_INVALID, "rt_framebuffer: image too large");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     if (width != c->W || height != c->H) {
         CK(cudaStreamSynchronize(c->stream));
         free_framebuffer(c);
@@ -485,7 +539,7 @@ int rt_framebuffer(rt_ctx *c, uint32_t width, uint32_t height)
 int rt_clear(rt_ctx *c)
 {
     if (!c || !c->d_accum) return fail(RT_ERR_INVALID, "rt_clear: no framebuffer");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     CK(cudaMemsetAsync(c->d_accum, 0, (size_t)c->W * c->H * 4 * sizeof(unsigned long long), c->stream));
     return RT_OK;
 }
@@ -508,7 +562,9 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     }
     const unsigned long long TP = (unsigned long long)tw * th;
     if (TP * p->spp >= (1ull << 31)) return fail(RT_ERR_INVALID, "rt_render: tile_pixels * spp must stay below 2^31; use smaller tiles or split spp with sample_base");
-    CK(cudaSetDevice(c->device));
+    const bool overlap = (p->flags & RT_FLAG_OVERLAP) != 0;
+    if (overlap) CK(cudaSetDevice(c->device));        // no join: this launch may run beside the chunks already queued
+    else CK(enter_ctx(c));
 
     const bool exact = (p->flags & RT_FLAG_EXACT) != 0;
     bool lbvh = false;
@@ -534,17 +590,41 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     EventPair ev;
     r = get_events(c, &ev);
     if (r) return r;
-    CK(cudaEventRecord(ev.a, c->stream));
+    cudaStream_t st = c->stream;
+    int aux_slot = -1;
+    if (overlap) {
+        const uint32_t band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP), nbands = (ntiles + band - 1u) / band;
+        if (c->counter_slot + nbands > kCounterRing) {   // the ring would be cleared inside this call: clear it now, behind every chunk still counting in it
+            CK(enter_ctx(c));
+            CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
+            c->counter_slot = 0;
+        }
+        if (ntiles > 1 && ntiles <= kTileRing && c->tile_ring_pos + ntiles > kTileRing) {   // same for the tile-list ring
+            CK(enter_ctx(c));
+            c->tile_ring_pos = 0;
+        }
+        CK(overlap_stream(c, &st, &aux_slot));
+    }
+    CK(cudaEventRecord(ev.a, st));
 
     uint4 *d_tiles = nullptr;
     uint4 tile0 = make_uint4(tiles[0].x0, tiles[0].y0, tiles[0].w, tiles[0].h);
+    bool tiles_from_pool = false;
     if (ntiles > 1) {
         static_assert(sizeof(rt_tile) == sizeof(uint4), "rt_tile must be 16 bytes");
-        CK(cudaMallocAsync((void **)&d_tiles, (size_t)ntiles * sizeof(uint4), c->stream));
+        if (ntiles <= kTileRing) {
+            // (without RT_FLAG_OVERLAP everything is on one stream and a wrapped slice is only rewritten behind its readers)
+            if (c->tile_ring_pos + ntiles > kTileRing) c->tile_ring_pos = 0;
+            d_tiles = c->d_tile_ring + c->tile_ring_pos;
+            c->tile_ring_pos += ntiles;
+        } else {
+            CK(cudaMallocAsync((void **)&d_tiles, (size_t)ntiles * sizeof(uint4), st));
+            tiles_from_pool = true;
+        }
         // pageable source: the runtime stages the bytes before returning, so `tiles` may be reused by the caller
-        CK(cudaMemcpyAsync(d_tiles, tiles, (size_t)ntiles * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(d_tiles, tiles, (size_t)ntiles * sizeof(uint4), cudaMemcpyHostToDevice, st));
     }
-    CK(rt_launch_add_count(c->d_accum, c->W, tile0, d_tiles, ntiles, (uint32_t)TP, p->spp, c->stream));
+    CK(rt_launch_add_count(c->d_accum, c->W, tile0, d_tiles, ntiles, (uint32_t)TP, p->spp, st));
     c->hs.launches += 1;
 
     RtRenderArgs a{};
@@ -573,7 +653,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         a.P = nt * (uint32_t)TP;
         a.total_items = a.P * p->spp;
         if (c->counter_slot == kCounterRing) {
-            CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), c->stream));
+            CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), st));
             c->counter_slot = 0;
         }
         a.work_counter = c->d_counter + c->counter_slot++;
@@ -583,15 +663,16 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
-        cudaError_t e = small ? rtf::launch_render_small(a, grid, c->stream)
-                        : tensor ? rtf::launch_render_tc(a, grid, smem, c->stream)
-                        : exact ? rtx::launch_render(a, grid, smem, c->stream, lbvh)
-                                : rtf::launch_render(a, grid, smem, c->stream, lbvh);
+        cudaError_t e = small ? rtf::launch_render_small(a, grid, st)
+                        : tensor ? rtf::launch_render_tc(a, grid, smem, st)
+                        : exact ? rtx::launch_render(a, grid, smem, st, lbvh)
+                                : rtf::launch_render(a, grid, smem, st, lbvh);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
     }
-    if (d_tiles) CK(cudaFreeAsync(d_tiles, c->stream));
-    CK(cudaEventRecord(ev.b, c->stream));
+    if (tiles_from_pool) CK(cudaFreeAsync(d_tiles, st));
+    CK(cudaEventRecord(ev.b, st));
+    if (aux_slot >= 0) { CK(cudaEventRecord(c->aux_tail[aux_slot], st)); c->aux_dirty[aux_slot] = true; }
     c->pending.push_back(ev);
     return RT_OK;
 }
@@ -666,7 +747,7 @@ int rt_primary_hits(rt_ctx *c, const rt_tile *tile, uint32_t flags, int32_t *sph
     if (tile->w == 0 || tile->h == 0) return RT_OK;
     if ((unsigned long long)tile->x0 + tile->w > c->W || (unsigned long long)tile->y0 + tile->h > c->H)
         return fail(RT_ERR_INVALID, "rt_primary_hits: tile outside the framebuffer");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     RtHitArgs a{};
     a.cam = c->cam;
     a.W = c->W; a.H = c->H; a.x0 = tile->x0; a.y0 = tile->y0; a.w = tile->w; a.h = tile->h;
@@ -680,7 +761,7 @@ int rt_closest_hits(rt_ctx *c, const float *rays6, uint64_t n, uint32_t flags, i
     if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_closest_hits: no scene uploaded");
     if (n == 0) return RT_OK;
     if (!rays6) return fail(RT_ERR_INVALID, "rt_closest_hits: rays is NULL");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     float *d_rays = nullptr;
     CK(cudaMalloc(&d_rays, n * 24));
     cudaError_t e = cudaMemcpyAsync(d_rays, rays6, n * 24, cudaMemcpyHostToDevice, c->stream);
@@ -695,7 +776,7 @@ int rt_closest_hits(rt_ctx *c, const float *rays6, uint64_t n, uint32_t flags, i
 int rt_resolve_device(rt_ctx *c)
 {
     if (!c || !c->d_accum) return fail(RT_ERR_INVALID, "rt_resolve_device: no framebuffer");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     CK(rt_launch_resolve(c->d_accum, (unsigned long long)c->W * c->H, c->d_rgb8, c->d_meanf, c->stream));
     c->hs.launches += 1;
     return RT_OK;
@@ -728,7 +809,7 @@ int rt_readback_f32(rt_ctx *c, float *dst)
 int rt_readback_accum(rt_ctx *c, uint64_t *dst)
 {
     if (!c || !dst || !c->d_accum) return fail(RT_ERR_INVALID, "rt_readback_accum: NULL argument or no framebuffer");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     CK(cudaMemcpyAsync(dst, c->d_accum, (size_t)c->W * c->H * 32, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return drain_events(c);
@@ -780,7 +861,7 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     if (spp_per_pass == 0) return fail(RT_ERR_INVALID, "rt_render_progressive: spp_per_pass must be > 0");
     if (!c->d_sph || !c->have_cam || !c->d_accum)
         return fail(RT_ERR_INVALID, "rt_render_progressive: scene, camera and framebuffer must be set first");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     const size_t bytes = (size_t)c->W * c->H * 3;
     const bool previews = cb && preview_every > 0;
     unsigned char *d_prev[2] = {nullptr, nullptr};
@@ -791,7 +872,7 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     cudaError_t e = cudaSuccess;
     auto cleanup = [&]() {
         if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < kAux; ++i) {
             if (d_prev[i]) cudaFree(d_prev[i]);
             if (h_prev[i]) cudaFreeHost(h_prev[i]);
             if (R[i]) cudaEventDestroy(R[i]);
@@ -893,7 +974,7 @@ int rt_write_ppm(const char *path, uint32_t width, uint32_t height, const uint8_
 int rt_fp32_peak_probe(rt_ctx *c, double out[3])
 {
     if (!c || !out) return fail(RT_ERR_INVALID, "rt_fp32_peak_probe: NULL argument");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     const int blocks = c->sm_count * 8, iters = 4096;
     cudaEvent_t a, b;
     CK(cudaEventCreate(&a));
@@ -921,7 +1002,7 @@ int rt_fp32_peak_probe(rt_ctx *c, double out[3])
 int rt_tf32_peak_probe(rt_ctx *c, double out[3])
 {
     if (!c || !out) return fail(RT_ERR_INVALID, "rt_tf32_peak_probe: NULL argument");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     const int blocks = c->sm_count, iters = 4096;
     cudaEvent_t a, b;
     CK(cudaEventCreate(&a));
@@ -964,7 +1045,7 @@ int rt_debug_sample_ball(rt_ctx *c, uint64_t n, uint64_t seed, int lens, float *
     if (!c || (n && !out_xyz)) return fail(RT_ERR_INVALID, "rt_debug_sample_ball: NULL argument");
     if (n == 0) return RT_OK;
     if (n > (1ull << 28)) return fail(RT_ERR_INVALID, "rt_debug_sample_ball: n too large");
-    CK(cudaSetDevice(c->device));
+    CK(enter_ctx(c));
     float *d = nullptr;
     CK(cudaMallocAsync((void **)&d, (size_t)n * 3u * sizeof(float), c->stream));
     cudaError_t e = rtf::launch_sample_ball(d, n, (uint32_t)seed, (uint32_t)(seed >> 32), lens, c->stream);

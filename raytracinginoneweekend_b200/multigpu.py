@@ -21,6 +21,8 @@ from __future__ import annotations
 
 import numpy as np
 
+FLAG_OVERLAP = 1 << 6   # RT_FLAG_OVERLAP (include/rt_api.h): a chunk may run beside the chunks queued before it
+
 
 def make_tiles(W: int, H: int, tw: int, th: int) -> np.ndarray:
     """Row-major grid of {x0,y0,w,h} tiles covering W x H; edge tiles are smaller."""
@@ -132,7 +134,8 @@ class CudaTileRenderer:
         self.spp, self.depth, self.seed, self.flags = spp, max_depth, seed, flags
 
     def render_tiles(self, tiles):
-        self.be.render_tiles(tiles, self.tw, self.th, self.spp, self.depth, self.seed, 0, self.flags)
+        # chunks of one frame are disjoint: let each launch start beside the tail of the previous one (RT_FLAG_OVERLAP)
+        self.be.render_tiles(tiles, self.tw, self.th, self.spp, self.depth, self.seed, 0, self.flags | FLAG_OVERLAP)
 
     def throttle(self, n):
         self.be.throttle(n)

@@ -13,7 +13,7 @@ import pytest
 
 from conftest import assert_bits_equal
 from raytracinginoneweekend_b200 import scenes
-from raytracinginoneweekend_b200.backend import (FLAG_BOOK_OPTICS, FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH,
+from raytracinginoneweekend_b200.backend import (FLAG_BOOK_OPTICS, FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH, FLAG_OVERLAP,
                                                  RtError)
 
 pytestmark = pytest.mark.gpu
@@ -134,6 +134,33 @@ def test_exact_render_tiles_and_sample_ranges_compose(be, port):
     # and the oracle agrees with the whole
     o = port.render(sc, W, H, spp, 50, 5, nthreads=64, rng=RNG_PHILOX, want_fixed=True)
     assert_bits_equal(full[..., :3], o["fixed"], "oracle")
+
+
+@pytest.mark.parametrize("flags", [FLAG_EXACT, 0, FLAG_LBVH], ids=["exact", "tensor", "lbvh"])
+def test_overlapped_chunks_equal_one_launch(be, flags):
+    """RT_FLAG_OVERLAP: chunk launches alternate between two internal streams and run beside each other; clear, readback
+    and non-overlapped renders on the context stay ordered around them without any call from the user.  Many small
+    chunks (more than the two streams, several frames) must give the accumulators of one launch, bit for bit."""
+    from raytracinginoneweekend_b200.multigpu import make_tiles
+    W, H, spp = 160, 96, 6
+    sc = scenes.huge_scene(W, H)
+    setup(be, sc, W, H)
+    tiles = make_tiles(W, H, 32, 16)
+    be.render_tiles(tiles, 32, 16, spp, 50, seed=9, flags=flags)
+    full = be.readback_accum()
+    for frame in range(3):
+        be.clear()                                            # ordered behind the previous frame's chunks
+        for s in range(0, len(tiles), 4):
+            be.render_tiles(tiles[s:s + 4], 32, 16, spp, 50, seed=9, flags=flags | FLAG_OVERLAP)
+        assert_bits_equal(be.readback_accum(), full, f"overlapped chunks, frame {frame}")   # no throttle / sync by the caller
+    # mixed: half the samples overlapped, the other half as a plain render of the whole frame
+    be.clear()
+    for s in range(0, len(tiles), 7):
+        be.render_tiles(tiles[s:s + 7], 32, 16, 3, 50, seed=9, flags=flags | FLAG_OVERLAP)
+    be.render(3, 50, seed=9, sample_base=3, flags=flags)
+    assert_bits_equal(be.readback_accum(), full, "overlapped + plain")
+    st = be.stats()
+    assert st["samples"] >= W * H * spp
 
 
 def test_fast_render_full_size_composition(be):
