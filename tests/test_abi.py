@@ -26,6 +26,19 @@ def test_header_symbols_are_exported():
     assert sorted(backend.EXPORTS) == names, "backend.EXPORTS must list exactly the header's entry points"
 
 
+def test_python_flags_match_the_header():
+    """backend.FLAG_* / multigpu.FLAG_OVERLAP are the RT_FLAG_* values of include/rt_api.h."""
+    from raytracinginoneweekend_b200 import backend, multigpu
+    text = open(os.path.join(ROOT, "include", "rt_api.h")).read()
+    header = {m.group(1): 1 << int(m.group(2)) for m in re.finditer(r"\bRT_FLAG_(\w+)\s*=\s*1u\s*<<\s*(\d+)", text)}
+    assert len(header) >= 7 and len(set(header.values())) == len(header)
+    mine = {"EXACT": backend.FLAG_EXACT, "ACCEL_BRUTE": backend.FLAG_BRUTE, "ACCEL_LBVH": backend.FLAG_LBVH,
+            "FILTER_FMA": backend.FLAG_FILTER_FMA, "FILTER_CHECK": backend.FLAG_FILTER_CHECK,
+            "BOOK_OPTICS": backend.FLAG_BOOK_OPTICS, "OVERLAP": backend.FLAG_OVERLAP}
+    assert mine == {k: header[k] for k in mine}
+    assert multigpu.FLAG_OVERLAP == header["OVERLAP"]
+
+
 def test_no_cpu_fallback():
     """Without a usable GPU rt_create must fail loudly (RT_ERR_NO_DEVICE), never render on the CPU."""
     import torch
