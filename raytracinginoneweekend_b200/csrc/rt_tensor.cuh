@@ -323,6 +323,12 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
     }
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
     const uint32_t nch = ns / RT_TC_CHUNK;
+#if RT_TC_STASH
+    // path state that the tile loop does not touch is parked here while the 64 accumulators of a tile are in registers
+    // (so that both halves of a tile can be loaded at once); [word][thread], at the end of the dynamic shared memory
+    uint32_t *s_stash = reinterpret_cast<uint32_t *>(mats_in_smem ? reinterpret_cast<unsigned char *>(s_meta + npad)
+                                                                   : reinterpret_cast<unsigned char *>(s_mat));
+#endif
 
     if (tid == 0) {
         for (int w = 0; w < RT_TC_WGS; ++w) {
@@ -506,8 +512,24 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 #endif
             uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
             best_t = FLT_MAX; best_i = -1;
+#if RT_TC_STASH
+            {
+                uint32_t *q = s_stash + tid;
+                q[0 * RT_TC_RAY_THREADS] = __float_as_uint(S.ar); q[1 * RT_TC_RAY_THREADS] = __float_as_uint(S.ag);
+                q[2 * RT_TC_RAY_THREADS] = __float_as_uint(S.ab); q[3 * RT_TC_RAY_THREADS] = S.pix;
+                q[4 * RT_TC_RAY_THREADS] = S.smp; q[5 * RT_TC_RAY_THREADS] = S.bounce;
+                q[6 * RT_TC_RAY_THREADS] = ts.samples; q[7 * RT_TC_RAY_THREADS] = ts.segments;
+                q[8 * RT_TC_RAY_THREADS] = ts.sky; q[9 * RT_TC_RAY_THREADS] = ts.absorbed;
+                q[10 * RT_TC_RAY_THREADS] = ts.capped; q[11 * RT_TC_RAY_THREADS] = pool.next;
+                q[12 * RT_TC_RAY_THREADS] = pool.end;
+            }
+#else
             const float ray_a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
             const float ray_inv_a = __frcp_rn(ray_a);
+#endif
+#if RT_TC_STASH
+#pragma unroll 1                                    // one loop body: both halves of a tile in disjoint registers, loaded back to back
+#endif
             for (uint32_t c = 0; c < nch; ++c) {
                 const uint32_t b = c % RT_TC_NBUF;
                 tc::bar_wait(bar + 1 + b, (full_parity >> b) & 1u);
@@ -591,6 +613,20 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 #endif
             }
             // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
+#if RT_TC_STASH
+            {
+                const uint32_t *q = s_stash + tid;
+                S.ar = __uint_as_float(q[0 * RT_TC_RAY_THREADS]); S.ag = __uint_as_float(q[1 * RT_TC_RAY_THREADS]);
+                S.ab = __uint_as_float(q[2 * RT_TC_RAY_THREADS]); S.pix = q[3 * RT_TC_RAY_THREADS];
+                S.smp = q[4 * RT_TC_RAY_THREADS]; S.bounce = q[5 * RT_TC_RAY_THREADS];
+                ts.samples = q[6 * RT_TC_RAY_THREADS]; ts.segments = q[7 * RT_TC_RAY_THREADS];
+                ts.sky = q[8 * RT_TC_RAY_THREADS]; ts.absorbed = q[9 * RT_TC_RAY_THREADS];
+                ts.capped = q[10 * RT_TC_RAY_THREADS]; pool.next = q[11 * RT_TC_RAY_THREADS];
+                pool.end = q[12 * RT_TC_RAY_THREADS];
+            }
+            const float ray_a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+            const float ray_inv_a = __frcp_rn(ray_a);
+#endif
             {
                 const float a = ray_a, inv_a = ray_inv_a;
 #if !(RT_TC_INLINE_PASS2 && RT_TC_MASK_POSITIVE)

@@ -149,6 +149,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_TC_AREADY_SLEEP
 #define RT_TC_AREADY_SLEEP 0       // > 0: the issuer backs off this many ns between polls while it waits for the ray rows
 #endif
+#ifndef RT_TC_STASH
+#define RT_TC_STASH 0              // 1: park 13 words of path state in shared memory across the tile loop (frees registers for the 64 accumulators)
+#endif
 #ifndef RT_TC_INLINE_PASS2
 #define RT_TC_INLINE_PASS2 0       // 1: run the candidate tests of a tile right after its sign masks (overlaps the next tile's MMAs)
 #endif
