@@ -903,6 +903,7 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     };
     while (done < p->spp && !stop) {
         rt_render_params q = *p;
+        q.flags &= ~(uint32_t)RT_FLAG_OVERLAP;        // passes cover the same pixels and previews are taken between them: keep stream order
         q.spp = (p->spp - done < spp_per_pass) ? (p->spp - done) : spp_per_pass;
         q.sample_base = p->sample_base + done;
         rc = rt_render(c, &full, &q);
