@@ -53,11 +53,15 @@ enum { RT_LAMBERT = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
 
 /* rt_render_params.flags / rt_primary_hits flags */
 enum {
-    RT_FLAG_EXACT = 1u << 0,      /* parity mode: no FMA contraction, the reference's operation order */
+    RT_FLAG_EXACT = 1u << 0,      /* parity mode: the reference's arithmetic and rejection sampler; renders are bit-identical to the
+                                     oracle.  48..1024 spheres, brute force: the tensor-core kernel with parity shading
+                                     (k_render_tc<true>); otherwise, or with RT_FLAG_FILTER_FMA, the straightforward parity kernels.
+                                     Without this flag the CLOSEST HIT is still the oracle's bit for bit (index, t, normal); only
+                                     the shading differs (unit-ball sampling by inversion, rsqrt / reciprocal normalisations) */
     RT_FLAG_ACCEL_BRUTE = 1u << 1,/* force brute-force closest hit (spheres staged in shared memory) */
     RT_FLAG_ACCEL_LBVH = 1u << 2, /* force the GPU-built LBVH */
-    RT_FLAG_FILTER_FMA = 1u << 3  /* brute force, throughput build: run the candidate filter on the FP32 FMA pipe instead of
-                                     the tensor cores (tcgen05 TF32x3 product, the default up to 1024 spheres); same image */,
+    RT_FLAG_FILTER_FMA = 1u << 3  /* brute force: run the candidate filter on the FP32 pipe instead of the tensor cores (tcgen05 TF32x3
+                                     product, the default for 48..1024 spheres); same accumulators, bit for bit */,
     RT_FLAG_FILTER_CHECK = 1u << 4,/* self-check: after the filtered closest hit, run the candidate test over ALL spheres and count
                                      the segments whose result differs in rt_stats.filter_misses (must stay 0; slow) */
     RT_FLAG_BOOK_OPTICS = 1u << 5 /* opt-in, NOT the reference's picture: textbook optics in place of the reference's quirks --
@@ -107,7 +111,21 @@ typedef struct rt_stats {
     double last_render_ms; /* device time of the most recent rt_render */
     double bvh_build_ms;   /* device time of the most recent LBVH build */
     uint64_t filter_misses;/* RT_FLAG_FILTER_CHECK: segments where the filtered closest hit differs from the unfiltered one */
+    uint32_t last_kernel;  /* rt_kernel_id of the most recent render launch (which kernel the dispatch chose) */
+    uint32_t reserved;
 } rt_stats;
+
+/* rt_stats.last_kernel */
+enum rt_kernel_id {
+    RT_KERNEL_NONE = 0,
+    RT_KERNEL_RENDER_PARITY = 1,     /* rtx::k_render: straightforward parity kernel, sign-mask filter on the ALU pipe */
+    RT_KERNEL_RENDER_FMA = 2,        /* rtf::k_render: FMA-chain candidate filter, throughput shading */
+    RT_KERNEL_RENDER_SMALL = 3,      /* rtf::k_render_small: <= 47 spheres, every sphere tested */
+    RT_KERNEL_RENDER_TC = 4,         /* rtf::k_render_tc<false>: tensor-core candidate filter, throughput shading (the timed default) */
+    RT_KERNEL_RENDER_TC_PARITY = 5,  /* rtf::k_render_tc<true>: the same kernel with the parity shading (bit-identical to the oracle) */
+    RT_KERNEL_RENDER_BVH_PARITY = 6, /* rtx::k_render_bvh */
+    RT_KERNEL_RENDER_BVH = 7         /* rtf::k_render_bvh */
+};
 
 RT_EXPORT const char *rt_last_error(void);
 RT_EXPORT const char *rt_version(void);

@@ -170,7 +170,7 @@ class RefOracle(_Base):
                                        i32p, fp, fp, C.c_int]
         L.ref_render.argtypes = [fp, u32p, C.c_uint32, fp, u32p, C.c_uint32, fp, C.c_uint32, C.c_uint32,
                                  C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
-                                 fp, dp, u64p, C.c_int]
+                                 fp, dp, u64p, C.c_int, C.c_uint32]
         L.ref_render.restype = C.c_double
         L.ref_sizes.argtypes = [u32p]
         L.ref_sizes.restype = C.c_int
@@ -197,8 +197,9 @@ class RefOracle(_Base):
                                   _p(idx, i32p), _p(t, fp), _p(nrm, fp), int(nthreads))
         return idx, t, nrm
 
-    def render(self, scene, W, H, spp, depth, seed, y0=0, rows=None, nthreads=1, want_sumsq=False):
-        rows = H - y0 if rows is None else rows
+    def render(self, scene, W, H, spp, depth, seed, y0=0, rows=None, nthreads=1, want_sumsq=False, ystep=1):
+        """rows y0, y0 + ystep, ... (`rows` of them; default: all rows from y0 with that stride)"""
+        rows = (H - y0 + ystep - 1) // ystep if rows is None else rows
         sph, sm, cam = _f32(scene.spheres), _u32(scene.sphere_mat), _f32(scene.camera)
         mats, mk = _f32(scene.materials), _u32(scene.mat_kind)
         total = np.zeros((rows, W, 3), _f)
@@ -206,7 +207,7 @@ class RefOracle(_Base):
         stats = np.zeros(4, np.uint64)
         secs = self.lib.ref_render(_p(sph, fp), _p(sm, u32p), sph.shape[0], _p(mats, fp), _p(mk, u32p), mats.shape[0],
                                    _p(cam, fp), W, H, y0, rows, spp, depth, int(seed),
-                                   _p(total, fp), _p(sumsq, dp), _p(stats, u64p), int(nthreads))
+                                   _p(total, fp), _p(sumsq, dp), _p(stats, u64p), int(nthreads), int(ystep))
         return dict(sum=total, sumsq=sumsq, stats=stats, seconds=secs)
 
     def save_ppm(self, path, rgb8):
@@ -230,7 +231,7 @@ class PortOracle(_Base):
         L.orc_render.argtypes = [fp, u32p, C.c_uint32, fp, u32p, C.c_uint32, fp, C.c_uint32, C.c_uint32,
                                  C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                  C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, C.c_int,
-                                 fp, dp, u64p, u64p, C.c_int]
+                                 fp, dp, u64p, u64p, C.c_int, C.c_uint32]
         L.orc_render.restype = C.c_double
         L.orc_resolve_fixed.argtypes = [u64p, C.c_uint64, C.c_uint32, fp, u8p]
         L.orc_philox.argtypes = [u32p, u32p, u32p]
@@ -253,8 +254,8 @@ class PortOracle(_Base):
         return idx, t, nrm
 
     def render(self, scene, W, H, spp, depth, seed, y0=0, rows=None, nthreads=1, want_sumsq=False,
-               x0=0, w=None, sample_base=0, rng=RNG_MT, want_fixed=False):
-        rows = H - y0 if rows is None else rows
+               x0=0, w=None, sample_base=0, rng=RNG_MT, want_fixed=False, ystep=1):
+        rows = (H - y0 + ystep - 1) // ystep if rows is None else rows
         w = W - x0 if w is None else w
         sph, sm, cam = _f32(scene.spheres), _u32(scene.sphere_mat), _f32(scene.camera)
         mats, mk = _f32(scene.materials), _u32(scene.mat_kind)
@@ -264,7 +265,7 @@ class PortOracle(_Base):
         stats = np.zeros(4, np.uint64)
         secs = self.lib.orc_render(_p(sph, fp), _p(sm, u32p), sph.shape[0], _p(mats, fp), _p(mk, u32p), mats.shape[0],
                                    _p(cam, fp), W, H, x0, y0, w, rows, spp, depth, int(seed), int(sample_base), int(rng),
-                                   _p(total, fp), _p(sumsq, dp), _p(fixed, u64p), _p(stats, u64p), int(nthreads))
+                                   _p(total, fp), _p(sumsq, dp), _p(fixed, u64p), _p(stats, u64p), int(nthreads), int(ystep))
         return dict(sum=total, sumsq=sumsq, fixed=fixed, stats=stats, seconds=secs)
 
     def resolve_fixed(self, fixed, spp):

@@ -309,7 +309,9 @@ void ref_primary_hits(const float *spheres, const std::uint32_t *sphere_mat, std
     for (auto &t_ : pool) t_.join();
 }
 
-// Full render of rows [y0, y0+rows) of a W x H image; the restated loop of src/main.cxx:191-215.
+// Full render of `rows` rows y0, y0 + ystep, y0 + 2 ystep, ... of a W x H image (ystep = 1: the band [y0, y0+rows));
+// the restated loop of src/main.cxx:191-215.  A strided row set is how bench.py takes a bounded, unbiased sample of a
+// frame in ONE call, so that every worker thread stays busy (rows are dealt to the threads one at a time).
 // Per row two generators are seeded: data.generator (jitter + materials) and the camera's private
 // one (lens).  Draw order per sample follows main.cxx:199-202: u-jitter, v-jitter, camera.ray, color.
 //   sum   : rows*W*3 float, sequential float sum of the spp radiance samples (std::reduce(seq), :205)
@@ -321,9 +323,10 @@ double ref_render(const float *spheres, const std::uint32_t *sphere_mat, std::ui
                   const float *cam, std::uint32_t W, std::uint32_t H,
                   std::uint32_t y0, std::uint32_t rows,
                   std::uint32_t spp, std::uint32_t depth, std::uint64_t seed,
-                  float *sum, double *sumsq, std::uint64_t *stats, int nthreads)
+                  float *sum, double *sumsq, std::uint64_t *stats, int nthreads, std::uint32_t ystep)
 {
     if (nthreads < 1) nthreads = 1;
+    if (ystep < 1) ystep = 1;
     scene_view sv{spheres, sphere_mat, n, materials, mat_kind, m};
     std::atomic<std::uint32_t> next{0};
     std::vector<std::array<std::uint64_t, 4>> tstats(nthreads, {0, 0, 0, 0});
@@ -337,7 +340,7 @@ double ref_render(const float *spheres, const std::uint32_t *sphere_mat, std::ui
         for (;;) {
             auto r = next.fetch_add(1);
             if (r >= rows) break;
-            auto y = y0 + r;
+            auto y = y0 + r * ystep;
             rd.generator = std::mt19937{mix_seed(seed, y, 0)};
             camera->generator = std::mt19937{mix_seed(seed, y, 1)};
             auto v = static_cast<float>(y) / static_cast<float>(H);

@@ -20,7 +20,10 @@ FLAG_LBVH = 1 << 2
 FLAG_FILTER_CHECK = 1 << 4  # count segments whose filtered closest hit differs from the unfiltered one (stats: filter_misses)
 FLAG_BOOK_OPTICS = 1 << 5   # opt-in textbook optics (Snell refraction, eye-relative camera rays, disk lens, [0,1] sky blend)
 FLAG_OVERLAP = 1 << 6       # rt_render_tiles: this chunk may run beside the chunks queued before it (disjoint tiles; two internal streams)
-FLAG_FILTER_FMA = 1 << 3   # throughput build: candidate filter on the FMA pipe instead of the tensor cores
+FLAG_FILTER_FMA = 1 << 3   # candidate filter on the FP32 pipe instead of the tensor cores
+# rt_stats.last_kernel (rt_kernel_id, include/rt_api.h)
+KERNEL_NAMES = {0: "none", 1: "rtx::k_render", 2: "rtf::k_render", 3: "rtf::k_render_small", 4: "rtf::k_render_tc<false>",
+                5: "rtf::k_render_tc<true>", 6: "rtx::k_render_bvh", 7: "rtf::k_render_bvh"}
 
 EXPORTS = [
     "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync", "rt_throttle",
@@ -54,7 +57,8 @@ class RtStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("segments", C.c_uint64), ("sphere_tests", C.c_uint64),
                 ("node_visits", C.c_uint64), ("sky", C.c_uint64), ("absorbed", C.c_uint64),
                 ("capped", C.c_uint64), ("launches", C.c_uint64), ("render_ms", C.c_double),
-                ("last_render_ms", C.c_double), ("bvh_build_ms", C.c_double), ("filter_misses", C.c_uint64)]
+                ("last_render_ms", C.c_double), ("bvh_build_ms", C.c_double), ("filter_misses", C.c_uint64),
+                ("last_kernel", C.c_uint32), ("reserved", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -81,6 +81,7 @@ struct rt_ctx {
     float *d_scratch = nullptr;
 
     void *h_pin = nullptr; size_t h_pin_bytes = 0;   // pinned staging for uploads / readbacks
+    void *d_hits = nullptr; size_t d_hits_bytes = 0; // grow-only scratch of rt_primary_hits / rt_closest_hits (index, t, normal, rays)
 
     // RT_FLAG_OVERLAP: chunk launches rotate over kAux auxiliary streams so that the tail of one persistent launch is
     // filled by the next; aux_tail[i] marks the end of the work queued on aux[i], aux_dirty[i] = c->stream has not waited for it
@@ -296,6 +297,7 @@ int rt_destroy(rt_ctx *c)
     if (c->bvh) rt_lbvh_destroy(c->bvh);
     cudaFree(c->d_counter); cudaFree(c->d_tile_ring); cudaFree(c->d_stats); cudaFree(c->d_scratch);
     if (c->h_pin) cudaFreeHost(c->h_pin);
+    cudaFree(c->d_hits);
     for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto &p : c->free_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -419,7 +421,7 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         // centres (keeps |c - g| small for the many small spheres whatever the ground sphere does).
         // Slots: 9 terms {xx,yy,zz,xy,xz,yz,x,y,z} x (f_h, f_l, f_h) | w_h, w_m, w_l | 1, 1 with
         // w = r^2 - |c|^2 + eps (|c|^2 + r^2); hi parts are TF32 (10-bit mantissa, round to nearest), evaluated in double.
-        // RT_TC_MASKMODE 0: column pos = 32 b + v holds sphere 32 b + 7 + 8 (v & 3) - (v >> 2), the I2IP sign-mask bit order.
+        // Column pos = 32 b + v holds sphere 32 b + (v < 16 ? 2 v : 2 (v - 16) + 1): the bit order of the I2IP.U2 sign masks.
         float *hb = (float *)(h + b_sph + b_rad + b_meta + b_mat + b_filt);
         std::memset(hb, 0, b_tcb);
         std::vector<float> med(n);
@@ -436,13 +438,7 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         };
         auto put = [&](uint32_t pos, uint32_t slot, float v) { hb[((size_t)(slot >> 2) * tc_ns + pos) * 4 + (slot & 3u)] = v; };
         for (uint32_t pos = 0; pos < tc_ns; ++pos) {
-#if RT_TC_MASKMODE == 0
-            const uint32_t v = pos & 31u, i = (pos & ~31u) + 7u + 8u * (v & 3u) - (v >> 2);
-#elif RT_TC_MASKMODE == 4
             const uint32_t v = pos & 31u, i = (pos & ~31u) + (v < 16u ? 2u * v : 2u * (v - 16u) + 1u);   // I2IP.U2 bit order
-#else
-            const uint32_t i = pos;                                     // sign masks in column order
-#endif
             if (i >= n) { put(pos, 27, -3.0e38f); continue; }           // padding: never a candidate
             const rt_sphere &sp = spheres[i];
             const double x = (double)sp.cx - g[0], y = (double)sp.cy - g[1], z = (double)sp.cz - g[2], r2 = (double)sp.r * sp.r;
@@ -573,7 +569,8 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     // throughput build, brute force: the candidate filter runs on the tensor cores unless the scene is too large
     // for the shared-memory sphere matrix or the caller asks for the FMA-pipe filter
     // (below RT_TC_MIN_SPHERES one 128-column tile is mostly padding and the FMA-pipe loop is shorter than the handshake)
-    const bool tensor = !exact && !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(p->flags & RT_FLAG_FILTER_FMA);
+    // (RT_FLAG_EXACT takes the same kernel with the parity shading; with RT_FLAG_FILTER_FMA it takes the rtx kernels)
+    const bool tensor = !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(p->flags & RT_FLAG_FILTER_FMA);
     bool smem_mats = false;
     size_t smem = tensor ? rt_render_tc_smem_bytes(c->npad, c->tc_ns, c->m, &smem_mats) : rt_render_smem_bytes(c->npad, c->nfilt, exact, lbvh);
     // throughput build, a handful of spheres: the one-path-per-thread kernel without filter code (k_render_small)
@@ -664,11 +661,15 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
         cudaError_t e = small ? rtf::launch_render_small(a, grid, st)
-                        : tensor ? rtf::launch_render_tc(a, grid, smem, st)
+                        : tensor ? rtf::launch_render_tc(a, grid, smem, st, exact)
                         : exact ? rtx::launch_render(a, grid, smem, st, lbvh)
                                 : rtf::launch_render(a, grid, smem, st, lbvh);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
+        c->hs.last_kernel = small ? RT_KERNEL_RENDER_SMALL
+                            : tensor ? (exact ? RT_KERNEL_RENDER_TC_PARITY : RT_KERNEL_RENDER_TC)
+                            : lbvh ? (exact ? RT_KERNEL_RENDER_BVH_PARITY : RT_KERNEL_RENDER_BVH)
+                                   : (exact ? RT_KERNEL_RENDER_PARITY : RT_KERNEL_RENDER_FMA);
     }
     if (tiles_from_pool) CK(cudaFreeAsync(d_tiles, st));
     CK(cudaEventRecord(ev.b, st));
@@ -707,36 +708,53 @@ int rt_render_tiles(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, uint32_t t
     return render_tiles_impl(c, tiles, ntiles, tile_w, tile_h, p);
 }
 
-static int hits_common(rt_ctx *c, RtHitArgs &a, unsigned long long total, uint32_t flags,
+// grow-only device scratch of the hit passes: [index i32 | t f32 | normal 3 x f32 | rays 6 x f32] x total
+static int hits_scratch(rt_ctx *c, size_t bytes)
+{
+    if (bytes <= c->d_hits_bytes) return RT_OK;
+    CK(cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_hits); c->d_hits = nullptr; c->d_hits_bytes = 0;
+    CK(cudaMalloc(&c->d_hits, bytes + bytes / 4));
+    c->d_hits_bytes = bytes + bytes / 4;
+    return RT_OK;
+}
+
+static int hits_common(rt_ctx *c, RtHitArgs &a, const float *rays6, unsigned long long total, uint32_t flags,
                        int32_t *sphere_index, float *t, float *normal_xyz)
 {
     const bool exact = (flags & RT_FLAG_EXACT) != 0;
     bool lbvh = false;
     int r = pick_accel(c, flags, &lbvh);
     if (r) return r;
-    int32_t *d_idx = nullptr; float *d_t = nullptr, *d_n = nullptr;
-    CK(cudaMalloc(&d_idx, total * 4));
-    CK(cudaMalloc(&d_t, total * 4));
-    CK(cudaMalloc(&d_n, total * 12));
+    r = hits_scratch(c, (size_t)total * (rays6 ? 44u : 20u));
+    if (r) return r;
+    int32_t *d_idx = (int32_t *)c->d_hits;
+    float *d_t = (float *)(d_idx + total), *d_n = d_t + total, *d_rays = d_n + 3 * total;
+    if (rays6) {
+        CK(cudaMemcpyAsync(d_rays, rays6, (size_t)total * 24, cudaMemcpyHostToDevice, c->stream));
+        a.rays = d_rays; a.nrays = total;
+    }
     a.sc = device_scene(c, lbvh);
     a.idx = d_idx; a.t = d_t; a.normal = d_n;
     a.stats = c->d_stats;
-    cudaError_t e = exact ? rtx::launch_hits(a, c->stream, lbvh) : rtf::launch_hits(a, c->stream, lbvh);
-    int rc = RT_OK;
-    if (e != cudaSuccess) rc = cuda_fail(e, "launch_hits");
-    c->hs.launches += 1;
-    if (!rc) {
-        cudaError_t e1 = cudaMemcpyAsync(sphere_index, d_idx, total * 4, cudaMemcpyDeviceToHost, c->stream);
-        cudaError_t e2 = cudaMemcpyAsync(t, d_t, total * 4, cudaMemcpyDeviceToHost, c->stream);
-        cudaError_t e3 = cudaMemcpyAsync(normal_xyz, d_n, total * 12, cudaMemcpyDeviceToHost, c->stream);
-        cudaError_t e4 = cudaStreamSynchronize(c->stream);
-        if (e1 != cudaSuccess) rc = cuda_fail(e1, "D2H idx");
-        else if (e2 != cudaSuccess) rc = cuda_fail(e2, "D2H t");
-        else if (e3 != cudaSuccess) rc = cuda_fail(e3, "D2H normal");
-        else if (e4 != cudaSuccess) rc = cuda_fail(e4, "sync");
+    // throughput build on a tensor-eligible scene: the closest hit of k_render_tc itself (k_hits_tc, rt_tensor.cuh)
+    const bool tensor = !exact && !lbvh && c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(flags & RT_FLAG_FILTER_FMA);
+    cudaError_t e;
+    if (tensor) {
+        const size_t smem = rt_render_tc_smem_bytes(c->npad, c->tc_ns, c->m, nullptr);
+        unsigned long long want = (total + RT_TC_WGS * 128ull - 1) / (RT_TC_WGS * 128ull);
+        int grid = (unsigned long long)c->sm_count > want ? (int)want : c->sm_count;
+        e = rtf::launch_hits_tc(a, grid < 1 ? 1 : grid, smem, c->stream);
+    } else {
+        e = exact ? rtx::launch_hits(a, c->stream, lbvh) : rtf::launch_hits(a, c->stream, lbvh);
     }
-    cudaFree(d_idx); cudaFree(d_t); cudaFree(d_n);
-    return rc;
+    if (e != cudaSuccess) return cuda_fail(e, "launch_hits");
+    c->hs.launches += 1;
+    CK(cudaMemcpyAsync(sphere_index, d_idx, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(t, d_t, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(normal_xyz, d_n, (size_t)total * 12, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return RT_OK;
 }
 
 int rt_primary_hits(rt_ctx *c, const rt_tile *tile, uint32_t flags, int32_t *sphere_index, float *t, float *normal_xyz)
@@ -752,7 +770,7 @@ int rt_primary_hits(rt_ctx *c, const rt_tile *tile, uint32_t flags, int32_t *sph
     a.cam = c->cam;
     a.W = c->W; a.H = c->H; a.x0 = tile->x0; a.y0 = tile->y0; a.w = tile->w; a.h = tile->h;
     a.rays = nullptr; a.nrays = 0;
-    return hits_common(c, a, (unsigned long long)tile->w * tile->h, flags, sphere_index, t, normal_xyz);
+    return hits_common(c, a, nullptr, (unsigned long long)tile->w * tile->h, flags, sphere_index, t, normal_xyz);
 }
 
 int rt_closest_hits(rt_ctx *c, const float *rays6, uint64_t n, uint32_t flags, int32_t *sphere_index, float *t, float *normal_xyz)
@@ -761,16 +779,10 @@ int rt_closest_hits(rt_ctx *c, const float *rays6, uint64_t n, uint32_t flags, i
     if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_closest_hits: no scene uploaded");
     if (n == 0) return RT_OK;
     if (!rays6) return fail(RT_ERR_INVALID, "rt_closest_hits: rays is NULL");
+    if (n >= (1ull << 32)) return fail(RT_ERR_INVALID, "rt_closest_hits: at most 2^32 - 1 rays per call");
     CK(enter_ctx(c));
-    float *d_rays = nullptr;
-    CK(cudaMalloc(&d_rays, n * 24));
-    cudaError_t e = cudaMemcpyAsync(d_rays, rays6, n * 24, cudaMemcpyHostToDevice, c->stream);
-    if (e != cudaSuccess) { cudaFree(d_rays); return cuda_fail(e, "H2D rays"); }
     RtHitArgs a{};
-    a.rays = d_rays; a.nrays = n;
-    int rc = hits_common(c, a, n, flags, sphere_index, t, normal_xyz);
-    cudaFree(d_rays);
-    return rc;
+    return hits_common(c, a, rays6, n, flags, sphere_index, t, normal_xyz);
 }
 
 int rt_resolve_device(rt_ctx *c)
@@ -864,15 +876,16 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     CK(enter_ctx(c));
     const size_t bytes = (size_t)c->W * c->H * 3;
     const bool previews = cb && preview_every > 0;
-    unsigned char *d_prev[2] = {nullptr, nullptr};
-    unsigned char *h_prev[2] = {nullptr, nullptr};
+    constexpr int kPrev = 2;                 // preview buffers in flight (device + pinned host)
+    unsigned char *d_prev[kPrev] = {nullptr, nullptr};
+    unsigned char *h_prev[kPrev] = {nullptr, nullptr};
     cudaStream_t copy = nullptr;
-    cudaEvent_t R[2] = {nullptr, nullptr}, Cv[2] = {nullptr, nullptr};
+    cudaEvent_t R[kPrev] = {nullptr, nullptr}, Cv[kPrev] = {nullptr, nullptr};
     int rc = RT_OK;
     cudaError_t e = cudaSuccess;
     auto cleanup = [&]() {
         if (copy) { cudaStreamSynchronize(copy); cudaStreamDestroy(copy); }
-        for (int i = 0; i < kAux; ++i) {
+        for (int i = 0; i < kPrev; ++i) {
             if (d_prev[i]) cudaFree(d_prev[i]);
             if (h_prev[i]) cudaFreeHost(h_prev[i]);
             if (R[i]) cudaEventDestroy(R[i]);
@@ -881,7 +894,7 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     };
     if (previews) {
         e = cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking);
-        for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        for (int i = 0; i < kPrev && e == cudaSuccess; ++i) {
             e = cudaMalloc((void **)&d_prev[i], bytes);
             if (e == cudaSuccess) e = cudaMallocHost((void **)&h_prev[i], bytes);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&R[i], cudaEventDisableTiming);
@@ -913,7 +926,7 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
         rc = deliver();
         if (rc) break;
         if (previews && !stop && (pass % preview_every == 0) && done < p->spp) {
-            const int i = (int)(nprev & 1u);
+            const int i = (int)(nprev % kPrev);
             e = rt_launch_resolve(c->d_accum, (unsigned long long)c->W * c->H, d_prev[i], nullptr, c->stream);
             if (e == cudaSuccess) e = cudaEventRecord(R[i], c->stream);
             if (e == cudaSuccess) e = cudaStreamWaitEvent(copy, R[i], 0);

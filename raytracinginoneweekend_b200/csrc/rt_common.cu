@@ -14,9 +14,6 @@ size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh
 size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns, uint32_t m, bool *mats_in_smem)
 {
     size_t b = 512 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * (RT_TC_WGS * 128u) * 4u;
-#if RT_TC_STASH
-    b += (size_t)13 * (RT_TC_WGS * 128u) * 4u;           // parked path state, at the end of whatever follows
-#endif
     const size_t extra = (size_t)m * 16u + (size_t)npad * 8u;
     const bool fits = b + extra <= RT_TC_SMEM_LIMIT;
     if (mats_in_smem) *mats_in_smem = fits;

@@ -1,9 +1,16 @@
-// rt_device.cuh -- device code of the path-tracing hot path, compiled TWICE:
-//   rt_kernels_exact.cu : -DRT_EXACT=1, nvcc --fmad=false  -> namespace rtx.  Every float operation is an
-//                         IEEE mul/add/div/sqrt in the reference's operation order; results are bit-identical
-//                         to the CPU oracle (oracle/rt_oracle.c) path by path.
-//   rt_kernels_fast.cu  : -DRT_EXACT=0, FMA contraction on  -> namespace rtf.  Same algorithm, fused
-//                         multiply-adds in the sphere loop; this is the throughput path.
+// rt_device.cuh -- device code of the path-tracing hot path, compiled TWICE, both times with nvcc --fmad=false
+// (the compiler never fuses a multiply and an add on its own; every fused multiply-add below is an explicit fmaf):
+//   rt_kernels_exact.cu : -DRT_EXACT=1 -> namespace rtx.  The straightforward parity kernels: every float operation is an
+//                         IEEE mul/add/div/sqrt in the reference's operation order; results are bit-identical to the CPU
+//                         oracle (oracle/rt_oracle.c) path by path.
+//   rt_kernels_fast.cu  : -DRT_EXACT=0 -> namespace rtf.  The throughput kernels.  The CLOSEST HIT is the same IEEE
+//                         arithmetic (a conservative filter -- tensor cores or explicit FMA chains -- only selects the
+//                         candidates; the reference test decides), so hit index, t and normal are bit-identical to the
+//                         oracle for the same ray.  Shading comes in two instantiations (template parameter PAR):
+//                         PAR = true is the parity arithmetic of rtx (rejection sampler, IEEE normalise / divide, Schlick in
+//                         double) and renders bit-identically to the oracle; PAR = false samples the unit ball by inversion
+//                         and uses rsqrt / reciprocal in the normalisations (the timed default; same law, checked
+//                         statistically).
 //
 // Reference semantics restated here (paths relative to the reference repo):
 //   intersect            src/raytracer.hxx:52-92      hit_world (first minimum)   src/raytracer.hxx:94-118
@@ -102,8 +109,12 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 __device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f; }
 __device__ __forceinline__ float s11(uint32_t w) { return (float)(w >> 8) * 5.9604644775390625e-8f * 2.f + -1.f; }
 
-#if !RT_EXACT
-// Throughput build: random_in_unit_sphere (src/raytracer.hxx:32-43) by inversion instead of rejection -- the same law
+#if RT_EXACT
+#define RT_PAR_DEFAULT true
+#else
+#define RT_PAR_DEFAULT false
+#endif
+// Throughput shading: random_in_unit_sphere (src/raytracer.hxx:32-43) by inversion instead of rejection -- the same law
 // (uniform in the unit ball) from three words: z/r uniform in [-1,1), azimuth uniform, radius U^(1/3).
 __device__ __forceinline__ void ball_by_inversion(uint32_t wz, uint32_t wphi, uint32_t wr, float &x, float &y, float &z)
 {
@@ -131,23 +142,23 @@ __device__ __forceinline__ void disk_by_inversion(uint32_t wrho, uint32_t wphi, 
     const float rho = sqrtf(u01(wrho));
     x = rho * cs; y = rho * sn;
 }
-#endif
 
 // ------------------------------------------------------------------ vector math in the reference's order
 __device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 // src/math.hxx:219-227
+template <bool PAR = RT_PAR_DEFAULT>
 __device__ __forceinline__ f3 normalize3(f3 a)
 {
-#if RT_EXACT
-    float len = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
-    if (fabsf(len) > FLT_MIN) { a.x = a.x / len; a.y = a.y / len; a.z = a.z / len; }
-#else
-    float len2 = a.x * a.x + a.y * a.y + a.z * a.z;
-    if (len2 > FLT_MIN * FLT_MIN * 0.f + 1.4e-38f) {   // length > FLT_MIN  <=>  len2 > FLT_MIN^2 (underflows: any normal len2)
-        float inv = rsqrtf(len2);
-        a.x *= inv; a.y *= inv; a.z *= inv;
+    if constexpr (PAR) {
+        float len = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
+        if (fabsf(len) > FLT_MIN) { a.x = a.x / len; a.y = a.y / len; a.z = a.z / len; }
+    } else {
+        float len2 = fmaf(a.z, a.z, fmaf(a.y, a.y, a.x * a.x));
+        if (len2 > 1.4e-38f) {                             // length > FLT_MIN: any normal len2
+            float inv = rsqrtf(len2);
+            a.x *= inv; a.y *= inv; a.z *= inv;
+        }
     }
-#endif
     return a;
 }
 // src/math.hxx:294-298
@@ -177,40 +188,35 @@ __device__ __forceinline__ f3 refract3_book(f3 I, f3 N, float eta)
     return mk3(I.x * eta - N.x * s, I.y * eta - N.y * s, I.z * eta - N.z * s);
 }
 // src/raytracer.hxx:45-50
+template <bool PAR = RT_PAR_DEFAULT>
 __device__ __forceinline__ float schlick(float ri, float cosine)
 {
-#if RT_EXACT
-    double q = (double)((1.f - ri) / (1.f + ri));
-    double r0 = q * q;
-    double x = (double)(1.f - cosine);
-    double x2 = x * x;
-    double x5 = x2 * x2 * x;
-    return (float)(r0 + (1. - r0) * x5);
-#else
-    float q = (1.f - ri) / (1.f + ri);
-    float r0 = q * q;
-    float x = 1.f - cosine;
-    float x2 = x * x;
-    return r0 + (1.f - r0) * (x2 * x2 * x);
-#endif
+    if constexpr (PAR) {
+        double q = (double)((1.f - ri) / (1.f + ri));
+        double r0 = q * q;
+        double x = (double)(1.f - cosine);
+        double x2 = x * x;
+        double x5 = x2 * x2 * x;
+        return (float)(r0 + (1. - r0) * x5);
+    } else {
+        float q = (1.f - ri) / (1.f + ri);
+        float r0 = q * q;
+        float x = 1.f - cosine;
+        float x2 = x * x;
+        return r0 + (1.f - r0) * (x2 * x2 * x);
+    }
 }
 
 // ------------------------------------------------------------------ closest hit, brute force
-// One sphere test: the arithmetic of src/raytracer.hxx:55-61.  In the fast TU the dot products are
-// explicit FMA chains (11 FP32 instructions instead of 18).
+// One sphere test: the arithmetic of src/raytracer.hxx:55-61, every operation a separate IEEE multiply / add in the
+// reference's order (both translation units are compiled with --fmad=false), s.w = radius * radius.
 __device__ __forceinline__ float sphere_disc(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
                                              float a, float &b)
 {
     float ocx = ox - s.x, ocy = oy - s.y, ocz = oz - s.z;
-#if RT_EXACT
     b = ocx * dx + ocy * dy + ocz * dz;
     float c = (ocx * ocx + ocy * ocy + ocz * ocz) - s.w;
     return b * b - a * c;
-#else
-    b = fmaf(ocz, dz, fmaf(ocy, dy, ocx * dx));
-    float c = fmaf(ocz, ocz, fmaf(ocy, ocy, fmaf(ocx, ocx, -s.w)));
-    return fmaf(b, b, -(a * c));
-#endif
 }
 
 // Exact per-candidate test (src/raytracer.hxx:63-89) against the running closest hit.  Candidates are
@@ -238,22 +244,6 @@ __device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, floa
 // Pass 2: each lane walks its own candidate bits (typically 3-10 of 488 spheres) and runs the exact
 //   reference test.  Lanes skip empty mask words independently, so the warp iterates max-over-lanes
 //   of the candidate COUNT, not the number of mask words.
-// The same test with the root chosen against tmax = FLT_MAX (exactly src/raytracer.hxx:63-89 as hit_world calls it),
-// returned instead of merged: FLT_MAX = no hit.  Merging with `if (t < best_t)` in increasing sphere order gives the
-// result of sphere_candidate_fast (a first root at or beyond best_t makes the second root lose as well), and two such
-// calls are independent, so their latencies overlap.
-__device__ __forceinline__ float sphere_root_fast(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
-                                                  float a, float inv_a)
-{
-    float b;
-    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
-    float sq;
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(fmaxf(disc, 0.f)));
-    const float t1 = (-b - sq) * inv_a, t2 = (sq - b) * inv_a;
-    const float t = (t1 > RT_KMIN) ? t1 : t2;
-    return (disc > 0.f && t > RT_KMIN && t < FLT_MAX) ? t : FLT_MAX;
-}
-
 // s_mask layout: [word][ray][thread] (conflict-free).
 template <int R>
 __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_sph, uint32_t n, uint32_t npad,
@@ -319,8 +309,8 @@ __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_s
 
 #if !RT_EXACT
 // ------------------------------------------------------------------ closest hit, brute force, throughput build
-// Pass 1 is a CONSERVATIVE candidate filter, pass 2 the reference test (with FMA contraction) on the few
-// candidates, so the hit that is returned is decided by the reference formula; the filter only has to
+// Pass 1 is a CONSERVATIVE candidate filter, pass 2 the reference test (sphere_candidate: the IEEE arithmetic of the
+// parity build) on the few candidates, so the hit that is returned is the oracle's bit for bit; the filter only has to
 // never drop a sphere the reference test would accept.
 //
 // With u = d/|d|:  disc/a = (oc.u)^2 - (|oc|^2 - r^2) = b^2 + 2 o.c + (r^2 - |c|^2) - |o|^2,  b = o.u - c.u.
@@ -363,22 +353,6 @@ __device__ __forceinline__ FastRay fast_ray_setup(const RtDeviceScene &sc, bool 
     return f;
 }
 
-// reference test (src/raytracer.hxx:55-89) with FMA contraction, approximate sqrt and a reciprocal of `a`
-__device__ __forceinline__ void sphere_candidate_fast(float4 s, int j, float ox, float oy, float oz,
-                                                      float dx, float dy, float dz, float a, float inv_a,
-                                                      float &best_t, int &best_i)
-{
-    float b;
-    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
-    if (disc > 0.f) {
-        float sq;
-        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(disc));
-        float t = (-b - sq) * inv_a;
-        if (!(t < best_t && t > RT_KMIN)) t = (sq - b) * inv_a;
-        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
-    }
-}
-
 // s_mask layout: [word][ray][thread]
 template <int R>
 __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, const float4 *__restrict__ s_sph,
@@ -403,10 +377,9 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
-            const float inv_a = __frcp_rn(a);
             if (live[r] && a > 0.f && a < 3.0e38f)
                 for (uint32_t j = 0; j < n; ++j)
-                    sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, best_t[r], best_i[r]);
+                    sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, best_t[r], best_i[r]);
         }
         return;
     }
@@ -440,7 +413,6 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
-            const float inv_a = __frcp_rn(a);
             uint32_t words = nz[r], cand = 0, w = 0;
             nz[r] = 0u;
             for (;;) {
@@ -453,7 +425,7 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
                 int lz = __clz(cand);                        // bit 23 (lz = 8) is the first sphere of the group
                 cand &= ~(0x80000000u >> lz);
                 uint32_t j = chunk + w * RT_FGROUP + (uint32_t)(lz - 8);
-                if (j < n) sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, best_t[r], best_i[r]);
+                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, best_t[r], best_i[r]);
             }
         }
     }
@@ -473,25 +445,13 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
 //     relative slack.  Culling uses tnear <= best_t (not <), so equal-t candidates with a lower index survive.
 struct BvhCounters { uint32_t nodes, leaves; };
 
-// Leaf test on a sphere record s = {centre, r*r} at sorted position pos.
+// Leaf test on a sphere record s = {centre, r*r} at sorted position pos: the reference test with the root chosen against
+// tmax = FLT_MAX (exactly src/raytracer.hxx:63-89 as hit_world calls it), merged in (t, index) order because leaves arrive
+// in tree order.  The original sphere index is only fetched for a root that can still win.
 __device__ __forceinline__ void bvh_leaf_sphere(const RtDeviceScene &sc, uint32_t pos, float4 s, float ox, float oy, float oz,
                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i, BvhCounters &cnt)
 {
     ++cnt.leaves;
-#if RT_BVH_FASTLEAF && !RT_EXACT
-    {   // the candidate test of the brute-force throughput kernels (reciprocal of a, approximate sqrt) + the (t, index) order;
-        // the original sphere index is only fetched when the root can still win
-        float inv_a;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_a) : "f"(a));
-        const float t = sphere_root_fast(s, ox, oy, oz, dx, dy, dz, a, inv_a);
-        if (t <= best_t && t < FLT_MAX) {
-            const int j = (int)__ldg(sc.bvh_prims + pos);
-            if (t < best_t || j < best_i) { best_t = t; best_i = j; }
-        }
-        return;
-    }
-#endif
-    int j = (int)__ldg(sc.bvh_prims + pos);
     float b;
     float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
     if (disc > 0.f) {
@@ -499,7 +459,10 @@ __device__ __forceinline__ void bvh_leaf_sphere(const RtDeviceScene &sc, uint32_
         float t = (-b - sq) / a;
         bool ok = t < FLT_MAX && t > RT_KMIN;
         if (!ok) { t = (-b + sq) / a; ok = t < FLT_MAX && t > RT_KMIN; }
-        if (ok && (t < best_t || (t == best_t && j < best_i))) { best_t = t; best_i = j; }
+        if (ok && t <= best_t) {
+            const int j = (int)__ldg(sc.bvh_prims + pos);
+            if (t < best_t || j < best_i) { best_t = t; best_i = j; }
+        }
     }
 }
 // leaf child `ref` of a node: the sphere comes from the sorted leaf array, or -- RT_BVH_LEAFINNODE -- from the node itself
@@ -535,7 +498,8 @@ __device__ __forceinline__ bool bvh_box(float lox, float loy, float loz, float h
     tn = fmaxf(tn, fminf(t0, t1)); tf = fminf(tf, fmaxf(t0, t1));
     tnear = tn;
     // relative slack on both ends; a negative tnear (origin inside) passes trivially
-    return tn - fabsf(tn) * 1e-5f <= tf + fabsf(tf) * 1e-5f && tf * 1.00001f >= RT_KMIN && tn - fabsf(tn) * 1e-5f <= best_t;
+    const float tn_lo = fmaf(fabsf(tn), -1e-5f, tn);
+    return tn_lo <= fmaf(fabsf(tf), 1e-5f, tf) && tf * 1.00001f >= RT_KMIN && tn_lo <= best_t;
 }
 
 // The same conservative test on a box stored as centre c, half extent h and hsum = hx + hy + hz (RT_BVH_CENTER):
@@ -549,14 +513,13 @@ __device__ __forceinline__ bool bvh_box_c(float cx, float cy, float cz, float hx
     const float dx = cx - ox, dy = cy - oy, dz = cz - oz;
     const float far = (fabsf(dx) + fabsf(dy)) + (fabsf(dz) + hsum);
     const float pad = fmaf(far, 9.765625e-4f, pad0);
-    const float mx = dx * ix, px = (hx + pad) * ix;
-    const float my = dy * iy, py = (hy + pad) * iy;
-    const float mz = dz * iz, pz = (hz + pad) * iz;
-    float tn = mx - fabsf(px), tf = mx + fabsf(px);
-    tn = fmaxf(tn, my - fabsf(py)); tf = fminf(tf, my + fabsf(py));
-    tn = fmaxf(tn, mz - fabsf(pz)); tf = fminf(tf, mz + fabsf(pz));
+    const float px = fabsf((hx + pad) * ix), py = fabsf((hy + pad) * iy), pz = fabsf((hz + pad) * iz);
+    float tn = fmaf(dx, ix, -px), tf = fmaf(dx, ix, px);
+    tn = fmaxf(tn, fmaf(dy, iy, -py)); tf = fminf(tf, fmaf(dy, iy, py));
+    tn = fmaxf(tn, fmaf(dz, iz, -pz)); tf = fminf(tf, fmaf(dz, iz, pz));
     tnear = tn;
-    return tn - fabsf(tn) * 1e-5f <= tf + fabsf(tf) * 1e-5f && tf * 1.00001f >= RT_KMIN && tn - fabsf(tn) * 1e-5f <= best_t;
+    const float tn_lo = fmaf(fabsf(tn), -1e-5f, tn);
+    return tn_lo <= fmaf(fabsf(tf), 1e-5f, tf) && tf * 1.00001f >= RT_KMIN && tn_lo <= best_t;
 }
 // both child boxes of a node (n0..n2 = the first three float4 of the node, hs = the two L1 half extents in centre form)
 #if RT_BVH_CENTER
@@ -664,7 +627,7 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // One shading pass for one path slot: finish the segment just traced (background / material), hand a new
 // camera sample to the slot if its path ended, draw the random numbers every lane needs in ONE shared
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
-template <bool LBVH>
+template <bool LBVH, bool PAR = RT_PAR_DEFAULT>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
                                            float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false,
                                            const float *__restrict__ s_rad = nullptr, const uint32_t *__restrict__ s_meta = nullptr,
@@ -684,7 +647,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
 
     if (!hold && S.st == ST_ACTIVE) {
         ++ts.segments;
-        unit = normalize3(mk3(S.dx, S.dy, S.dz));                        // ray::unit_direction, src/math.hxx:351
+        unit = normalize3<PAR>(mk3(S.dx, S.dy, S.dz));                   // ray::unit_direction, src/math.hxx:351
         if (best_i < 0) {                                                // miss: src/main.cxx:71 (quirk F6: + 1.f)
             float t = .5f * unit.y + (A.book ? .5f : 1.f);              // book optics: the usual [0,1] blend
             float omt = 1.f - t;
@@ -705,12 +668,12 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             m = s_mat ? s_mat[meta & 0x3fffffffu] : __ldg(sc.mat + (meta & 0x3fffffffu));
             kind = (int)(meta >> 30);
             p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
-#if RT_EXACT
-            n = mk3((p.x - s.x) / rad, (p.y - s.y) / rad, (p.z - s.z) / rad);            // src/raytracer.hxx:70
-#else
-            float inv_rad = __frcp_rn(rad);
-            n = mk3((p.x - s.x) * inv_rad, (p.y - s.y) * inv_rad, (p.z - s.z) * inv_rad);
-#endif
+            if constexpr (PAR) {
+                n = mk3((p.x - s.x) / rad, (p.y - s.y) / rad, (p.z - s.z) / rad);        // src/raytracer.hxx:70
+            } else {
+                float inv_rad = __frcp_rn(rad);
+                n = mk3((p.x - s.x) * inv_rad, (p.y - s.y) * inv_rad, (p.z - s.z) * inv_rad);
+            }
             if (kind == 0) mode = RM_BALL;
             else if (kind == 1) { refl = reflect3(unit, n); mode = RM_BALL; }
             else {                                                        // dielectric, src/raytracer.hxx:158-178
@@ -723,7 +686,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
                     cosine = cosine * -1.f;
                 }
                 refr = A.book ? refract3_book(unit, outward, ri) : refract3(unit, outward, ri);
-                if (refr.x * refr.x + refr.y * refr.y + refr.z * refr.z > 0.f) prob = schlick(ri, cosine);
+                if (refr.x * refr.x + refr.y * refr.y + refr.z * refr.z > 0.f) prob = schlick<PAR>(ri, cosine);
                 refl = reflect3(unit, n);
                 mode = RM_UNIFORM;
             }
@@ -767,10 +730,11 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         if (!__any_sync(RT_FULL, need)) break;
     }
 
-#if RT_EXACT
-    // ---- one Philox loop serves camera jitter, lens / lambert / metal ball samples and the dielectric coin
     float r0 = 0.f, r1 = 0.f, r2 = 0.f, ju = 0.f, jv = 0.f;
     const bool camera_lane = (mode == RM_CAMERA);
+    if constexpr (PAR) {
+    // ---- parity shading: one Philox loop serves camera jitter, lens / lambert / metal ball samples (the reference's
+    // rejection loop, src/raytracer.hxx:32-43, one block per attempt) and the dielectric coin
     uint32_t blk = 0;
     while (mode != RM_NONE) {
         uint4 w = philox4x32_10(S.pix, S.smp, ev, blk, A.key0, A.key1);
@@ -784,25 +748,18 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
         } else {                                                          // src/raytracer.hxx:32-43
             r0 = s11(w.x); r1 = s11(w.y); r2 = s11(w.z);
             if (camera_lane && A.book) r2 = 0.f;                          // book optics: the lens sample is a DISK point
-#if RT_EXACT
             bool reject = sqrtf(r0 * r0 + r1 * r1 + r2 * r2) > 1.f;
-#else
-            bool reject = (r0 * r0 + r1 * r1 + r2 * r2) > 1.f;
-#endif
             if (reject) ++blk; else mode = RM_NONE;
         }
     }
-
-#else
-    // ---- throughput build: ONE Philox block per lane and no rejection loop.  random_in_unit_sphere
+    } else {
+    // ---- throughput shading: ONE Philox block per lane and no rejection loop.  random_in_unit_sphere
     // (src/raytracer.hxx:32-43) returns a point uniform in the unit ball; the same distribution is drawn by inversion
     // (z uniform in [-1,1), azimuth uniform, radius U^(1/3)), which costs one block instead of a loop that runs for
     // the slowest lane of the warp (mean 1.9 attempts per lane, ~5.5 for the maximum over 32 lanes).  The lens offset
     // uses only x and y of the ball point (src/camera.hxx:51-53); their joint law is rho = sqrt(1 - U^(2/3)) with a
     // uniform azimuth, so the camera ray needs the two words the pixel jitter leaves over.
-    // The parity build above keeps the reference's rejection loop word for word; the two are compared statistically.
-    float r0 = 0.f, r1 = 0.f, r2 = 0.f, ju = 0.f, jv = 0.f;
-    const bool camera_lane = (mode == RM_CAMERA);
+    // The parity shading above keeps the reference's rejection loop word for word; the two are compared statistically.
     if (mode != RM_NONE) {
         const uint4 w = philox4x32_10(S.pix, S.smp, ev, 0u, A.key0, A.key1);
         if (camera_lane) {
@@ -814,7 +771,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             if (mode == RM_UNIFORM) r0 = u01(w.x);                        // the dielectric coin is word 0, as in the parity build
         }
     }
-#endif
+    }
 
     // ---- next ray
     if (camera_lane) {                                                    // src/main.cxx:192-200, src/camera.hxx:46-57
@@ -936,10 +893,9 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
                 for (int r = 0; r < RT_RPT; ++r) {
                     if (!live[r]) continue;
                     const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
-                    const float inv_a = __frcp_rn(a);
                     float ct = FLT_MAX; int ci = -1;
                     for (uint32_t j = 0; j < A.sc.n; ++j)
-                        sphere_candidate_fast(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, inv_a, ct, ci);
+                        sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, ct, ci);
                     if (ci != best_i[r] || ct != best_t[r]) atomicAdd(A.stats + 7, 1ull);
                 }
             }
@@ -999,9 +955,8 @@ __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(cons
         best_t = FLT_MAX; best_i = -1;
         const float a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
         if (S.st == ST_ACTIVE && a > 0.f && a < 3.0e38f) {
-            const float inv_a = __frcp_rn(a);
             for (uint32_t j = 0; j < n; ++j)
-                sphere_candidate_fast(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, inv_a, best_t, best_i);
+                sphere_candidate(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, best_t, best_i);
         }
     }
     uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
@@ -1018,14 +973,52 @@ __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(cons
 }
 #endif
 
+// ------------------------------------------------------------------ parity pass helpers (k_hits, k_hits_tc)
+// ray i of the pass: caller-supplied, or the primary ray of pixel i of the tile: u = x/W, v = y/H, lens offset 0
+// (src/main.cxx:192-195 without jitter, src/camera.hxx:56)
+__device__ __forceinline__ void hits_ray(const RtHitArgs &A, unsigned long long i, float &ox, float &oy, float &oz,
+                                         float &dx, float &dy, float &dz)
+{
+    if (A.rays) {
+        const float *r = A.rays + 6ull * i;
+        ox = r[0]; oy = r[1]; oz = r[2]; dx = r[3]; dy = r[4]; dz = r[5];
+    } else {
+        uint32_t ty = (uint32_t)(i / A.w), tx = (uint32_t)(i - (unsigned long long)ty * A.w);
+        float u = (float)(A.x0 + tx) / (float)A.W;
+        float v = (float)(A.y0 + ty) / (float)A.H;
+        float omv = 1.f - v;
+        const RtDeviceCamera &c = A.cam;
+        ox = c.ox; oy = c.oy; oz = c.oz;
+        dx = (c.llx + c.hx * u) + c.vx * omv;
+        dy = (c.lly + c.hy * u) + c.vy * omv;
+        dz = (c.llz + c.hz * u) + c.vz * omv;
+    }
+}
+// hit record of src/raytracer.hxx:66-72: index, t, normal = (o + d t - c) / r (s = the sphere record when bi >= 0)
+__device__ __forceinline__ void hits_store(const RtHitArgs &A, unsigned long long i, int bi, float bt, float4 s,
+                                           float ox, float oy, float oz, float dx, float dy, float dz)
+{
+    A.idx[i] = bi;
+    if (bi >= 0) {
+        float rad = __ldg(A.sc.sph_rad + bi);
+        float px = ox + dx * bt, py = oy + dy * bt, pz = oz + dz * bt;
+        A.t[i] = bt;
+        A.normal[3 * i + 0] = (px - s.x) / rad;
+        A.normal[3 * i + 1] = (py - s.y) / rad;
+        A.normal[3 * i + 2] = (pz - s.z) / rad;
+    } else {
+        A.t[i] = 0.f;
+        A.normal[3 * i + 0] = 0.f; A.normal[3 * i + 1] = 0.f; A.normal[3 * i + 2] = 0.f;
+    }
+}
+
 #if !RT_EXACT
 #include "rt_tensor.cuh"
 #endif
 #include "rt_bvh_render.cuh"
 
 // ------------------------------------------------------------------ parity pass: primary / caller-supplied rays
-// One thread per ray; the same two-pass brute-force closest hit.  Primary rays: u = x/W, v = y/H, lens
-// offset 0 (src/main.cxx:192-195 without jitter, src/camera.hxx:56).
+// One thread per ray; the same two-pass brute-force closest hit (or the LBVH) as the render kernels of this build.
 template <bool LBVH>
 __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtHitArgs A)
 {
@@ -1055,22 +1048,7 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
         unsigned long long i = it * stride + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
         bool live[1] = {i < total};
         float ox[1] = {0.f}, oy[1] = {0.f}, oz[1] = {0.f}, dx[1] = {0.f}, dy[1] = {0.f}, dz[1] = {0.f};
-        if (live[0]) {
-            if (A.rays) {
-                const float *r = A.rays + 6ull * i;
-                ox[0] = r[0]; oy[0] = r[1]; oz[0] = r[2]; dx[0] = r[3]; dy[0] = r[4]; dz[0] = r[5];
-            } else {
-                uint32_t ty = (uint32_t)(i / A.w), tx = (uint32_t)(i - (unsigned long long)ty * A.w);
-                float u = (float)(A.x0 + tx) / (float)A.W;
-                float v = (float)(A.y0 + ty) / (float)A.H;
-                float omv = 1.f - v;
-                const RtDeviceCamera &c = A.cam;
-                ox[0] = c.ox; oy[0] = c.oy; oz[0] = c.oz;
-                dx[0] = (c.llx + c.hx * u) + c.vx * omv;
-                dy[0] = (c.lly + c.hy * u) + c.vy * omv;
-                dz[0] = (c.llz + c.hz * u) + c.vz * omv;
-            }
-        }
+        if (live[0]) hits_ray(A, i, ox[0], oy[0], oz[0], dx[0], dy[0], dz[0]);
         float bt[1]; int bi[1];
         if (LBVH) {
             closest_hit_lbvh(A.sc, live[0], ox[0], oy[0], oz[0], dx[0], dy[0], dz[0], bt[0], bi[0], cnt);
@@ -1081,21 +1059,9 @@ __global__ void __launch_bounds__(RT_THREADS) k_hits(const __grid_constant__ RtH
             closest_hit_brute_fast<1>(A.sc, s_sph, s_filt, s_mask, live, ox, oy, oz, dx, dy, dz, bt, bi);
 #endif
         }
-        if (live[0]) {
-            A.idx[i] = bi[0];
-            if (bi[0] >= 0) {
-                float4 s = LBVH ? __ldg(A.sc.sph + bi[0]) : s_sph[bi[0]];
-                float rad = __ldg(A.sc.sph_rad + bi[0]);
-                float px = ox[0] + dx[0] * bt[0], py = oy[0] + dy[0] * bt[0], pz = oz[0] + dz[0] * bt[0];
-                A.t[i] = bt[0];
-                A.normal[3 * i + 0] = (px - s.x) / rad;
-                A.normal[3 * i + 1] = (py - s.y) / rad;
-                A.normal[3 * i + 2] = (pz - s.z) / rad;
-            } else {
-                A.t[i] = 0.f;
-                A.normal[3 * i + 0] = 0.f; A.normal[3 * i + 1] = 0.f; A.normal[3 * i + 2] = 0.f;
-            }
-        }
+        if (live[0])
+            hits_store(A, i, bi[0], bt[0], bi[0] < 0 ? make_float4(0.f, 0.f, 0.f, 0.f) : LBVH ? __ldg(A.sc.sph + bi[0]) : s_sph[bi[0]],
+                       ox[0], oy[0], oz[0], dx[0], dy[0], dz[0]);
     }
     if (LBVH) {
         uint32_t v[2] = {cnt.nodes, cnt.leaves};

@@ -104,7 +104,8 @@ cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
 namespace rtf {
-cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool parity);
+cudaError_t launch_hits_tc(const RtHitArgs &a, int grid, size_t smem, cudaStream_t s);
 cudaError_t launch_render_small(const RtRenderArgs &a, int grid, cudaStream_t s);
 cudaError_t small_occupancy(int *ctas_per_sm);
 cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, uint32_t key1, int lens, cudaStream_t s);
@@ -125,12 +126,6 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_BVH_LEAFINNODE
 #define RT_BVH_LEAFINNODE 1 // 1 (needs RT_BVH_CENTER): the child slot of a leaf holds the sphere (centre, |r|) instead of its box; the leaf test reads no memory
 #endif
-#ifndef RT_BVH_FASTLEAF
-#define RT_BVH_FASTLEAF 1   // 1: throughput build: LBVH leaves run the reciprocal / approximate-sqrt candidate test of the brute-force kernels
-#endif
-#ifndef RT_TC_PASS2_PAIR
-#define RT_TC_PASS2_PAIR 0      // tensor kernel: 1 = the candidate loop tests two candidates per iteration (measured: 1.805 vs 1.816 Gsamples/s, not kept)
-#endif
 #ifndef RT_TC_WGS
 #define RT_TC_WGS 5
 #endif
@@ -140,29 +135,8 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_TC_NBUF
 #define RT_TC_NBUF 1
 #endif
-#ifndef RT_TC_SELFISSUE
-#define RT_TC_SELFISSUE 0          // 1: no issuer warps -- the last ray warp to arrive (shared-memory arrival counter) issues the tile's MMAs
-#endif
-#ifndef RT_TC_NOVOTE
-#define RT_TC_NOVOTE 0             // 1: no per-pass warpgroup vote (bar.red) -- finished warps are counted and the issuer ends the warpgroup
-#endif
-#ifndef RT_TC_AREADY_SLEEP
-#define RT_TC_AREADY_SLEEP 0       // > 0: the issuer backs off this many ns between polls while it waits for the ray rows
-#endif
-#ifndef RT_TC_STASH
-#define RT_TC_STASH 0              // 1: park 13 words of path state in shared memory across the tile loop (frees registers for the 64 accumulators)
-#endif
-#ifndef RT_TC_INLINE_PASS2
-#define RT_TC_INLINE_PASS2 0       // 1: run the candidate tests of a tile right after its sign masks (overlaps the next tile's MMAs)
-#endif
-#ifndef RT_TC_MASKMODE
-#define RT_TC_MASKMODE 4          // sign-mask reduction of the accumulators (tc::sign_mask): 0 I2IP.U8, 1 FMA pipe, 2 ALU pipe, 3 both, 4 I2IP.U2
-#endif
-#define RT_TC_MASK_POSITIVE (RT_TC_MASKMODE == 0 || RT_TC_MASKMODE == 4)
-#if RT_TC_MASK_POSITIVE
-#define RT_TC_NEG 1.f             // accumulators hold +q, columns permuted to the I2IP bit order
-#else
-#define RT_TC_NEG -1.f            // accumulators hold -q (sign bit = candidate), columns in sphere order
+#ifndef RT_TC_RAY_HINT
+#define RT_TC_RAY_HINT 0           // > 0: suspend-time hint (ns) of the ray warps' try_wait on an accumulator tile; 0 = bare spin
 #endif
 #define RT_TC_EPS 1.52587890625e-5   // 2^-16: relative inflation of the tensor filter (measured error < 2^-20.4)
 #ifndef RT_TC_MIN_SPHERES

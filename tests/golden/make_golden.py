@@ -21,7 +21,7 @@ from oracle.loader import RefOracle  # noqa: E402
 from raytracinginoneweekend_b200 import scenes  # noqa: E402
 
 OUT = os.path.dirname(os.path.abspath(__file__))
-NTHREADS = os.cpu_count() or 1
+NTHREADS = int(os.environ.get("GOLDEN_THREADS", os.cpu_count() or 1))
 
 
 def kat(R: RefOracle):
@@ -124,14 +124,37 @@ def reference_renders(R: RefOracle):
     np.savez_compressed(os.path.join(OUT, "reference_render.npz"), **out)
 
 
+def reference_renders_full(R: RefOracle):
+    """The same at the size SURVEY section 8(c)(iii) asks for: 640x360 (a quarter of BASELINE's 1280x720 frame, same
+    aspect and camera), huge scene 256 spp, simple scene 1024 spp, depth 50.  About 2 700 core-seconds.  The variance
+    is stored as float16 (three digits are plenty for a noise bound) to keep the fixture small."""
+    out = {}
+    for name, W, H, spp in (("simple", 640, 360, 1024), ("huge", 640, 360, 256)):
+        sc = scenes.get_scene(name, W, H)
+        r = R.render(sc, W, H, spp, 50, 777, nthreads=NTHREADS, want_sumsq=True)
+        mean = r["sum"].astype(np.float64) / spp
+        var = np.maximum(r["sumsq"] / spp - mean * mean, 0.0) * spp / (spp - 1)
+        out[f"{name}_mean"] = mean.astype(np.float32)
+        out[f"{name}_var"] = np.minimum(var, 6.0e4).astype(np.float16)
+        out[f"{name}_cfg"] = np.array([W, H, spp, 50, 777])
+        out[f"{name}_stats"] = r["stats"]
+        print(name, "seconds", r["seconds"], "stats", r["stats"], "segments/sample", r["stats"][0] / (W * H * spp), flush=True)
+    np.savez_compressed(os.path.join(OUT, "reference_render_640.npz"), **out)
+
+
 if __name__ == "__main__":
     if not RefOracle.available():
         raise SystemExit("oracle/_ref/libref_oracle.so missing: run `bash oracle/build_ref.sh` where /root/reference exists")
     R = RefOracle()
+    if "--full-only" in sys.argv:          # only the big statistical fixture (minutes of CPU)
+        reference_renders_full(R)
+        raise SystemExit(0)
     kat(R)
     primary(R)
     small_renders(R)
     reference_renders(R)
+    if "--full" in sys.argv:
+        reference_renders_full(R)
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -2,11 +2,14 @@
 (librtiow_b200.so via ctypes); the CPU oracle is only the checker.
 
 Bars (BASELINE.json north_star):
-  * primary rays, 1 spp, no jitter: hit sphere index bit-exact, t / normal within 1e-5 relative
-    (the exact mode is expected -- and asserted -- to be 0 ulp);
+  * primary rays, 1 spp, no jitter: hit sphere index bit-exact, t / normal within 1e-5 relative -- asserted at 0 ulp
+    for EVERY closest-hit path of the library, the timed ones first: the tensor-core kernel's closest hit (flags = 0 on
+    a 48..1024-sphere scene: k_hits_tc calls the very function k_render_tc calls), the FMA-chain filter, the
+    all-spheres loop of the small-scene kernel, the LBVH, and the straightforward parity kernels;
   * full renders: per-pixel RMSE and mean luminance within the Monte Carlo noise bound against the
-    reference CPU render; in exact mode, additionally BIT-EXACT accumulators against the oracle port
-    driven by the same counter-based RNG.
+    reference CPU render; with RT_FLAG_EXACT (parity shading: the reference's rejection sampler and IEEE normalisations)
+    additionally BIT-EXACT accumulators against the oracle port driven by the same counter-based RNG -- on the
+    tensor-core kernel too (k_render_tc<true>).
 """
 import numpy as np
 import pytest
@@ -14,7 +17,11 @@ import pytest
 from conftest import assert_bits_equal
 from raytracinginoneweekend_b200 import scenes
 from raytracinginoneweekend_b200.backend import (FLAG_BOOK_OPTICS, FLAG_BRUTE, FLAG_EXACT, FLAG_FILTER_CHECK, FLAG_FILTER_FMA, FLAG_LBVH, FLAG_OVERLAP,
-                                                 RtError)
+                                                 KERNEL_NAMES, RtError)
+
+# every closest-hit path: (flags, id)
+HIT_PATHS = [(0, "throughput-default"), (FLAG_FILTER_FMA, "throughput-fma-filter"), (FLAG_LBVH, "throughput-lbvh"),
+             (FLAG_EXACT, "parity"), (FLAG_EXACT | FLAG_LBVH, "parity-lbvh")]
 
 pytestmark = pytest.mark.gpu
 
@@ -34,10 +41,20 @@ def test_primary_hits_match_reference_fixture(be, golden):
     for name in ("huge", "simple"):
         W, H = (int(x) for x in g[f"{name}_wh"])
         setup(be, scenes.get_scene(name, W, H).with_camera(aperture=0.0), W, H)
-        idx, t, nrm = be.primary_hits(flags=FLAG_EXACT)
-        assert_bits_equal(idx.astype(np.int16), g[f"{name}_idx"], f"{name} hit index")
-        assert_bits_equal(t, g[f"{name}_t"], f"{name} t")
-        assert_bits_equal(nrm, g[f"{name}_n"], f"{name} normal")
+        for flags, what in HIT_PATHS:
+            idx, t, nrm = be.primary_hits(flags=flags)
+            assert_bits_equal(idx.astype(np.int16), g[f"{name}_idx"], f"{name} hit index ({what})")
+            assert_bits_equal(t, g[f"{name}_t"], f"{name} t ({what})")
+            assert_bits_equal(nrm, g[f"{name}_n"], f"{name} normal ({what})")
+
+
+def test_camera_state_matches_reference(be, golden):
+    """Row a1: rt_camera_set derives {origin, lower-left corner, horizontal, vertical, lens radius} exactly as the
+    reference constructor does (src/camera.hxx:24-44); fixture from the compiled reference."""
+    g = golden("kat")
+    for ci, cam in enumerate(g["cams"]):
+        be.set_camera(cam)
+        assert_bits_equal(be.camera_state(), g["cam_state"][ci], f"camera {ci}")
 
 
 def test_primary_hits_config2_full_size(be, port):
@@ -46,22 +63,20 @@ def test_primary_hits_config2_full_size(be, port):
     W, H = 1280, 720
     sc = scenes.huge_scene(W, H).with_camera(aperture=0.0)
     setup(be, sc, W, H)
-    idx, t, nrm = be.primary_hits(flags=FLAG_EXACT)
     oi, ot, on = port.primary_hits(sc, W, H, nthreads=64)
-    assert_bits_equal(idx, oi, "hit index")
-    rel_t = np.abs(t - ot) / np.maximum(np.abs(ot), 1e-30)
-    rel_n = np.abs(nrm - on) / np.maximum(np.abs(on), 1e-30)
-    assert rel_t.max() <= 1e-5 and rel_n.max() <= 1e-5     # the stated tolerance
-    assert_bits_equal(t, ot, "t")                            # ... and in fact 0 ulp
-    assert_bits_equal(nrm, on, "normal")
-    assert len(np.unique(idx)) > 100 and (idx < 0).any()
-    # the throughput (FMA) build must agree on (nearly) every pixel; differences can only sit on silhouettes
-    fi, ft, fn = be.primary_hits(flags=0)
-    assert (fi != oi).mean() < 2e-4
-    # tiles of the same pass
-    ti, tt, tn = be.primary_hits(tile=(37, 11, 501, 97), flags=FLAG_EXACT)
-    assert_bits_equal(ti, oi[11:108, 37:538], "tile hit index")
-    assert_bits_equal(tt, ot[11:108, 37:538], "tile t")
+    assert len(np.unique(oi)) > 100 and (oi < 0).any()
+    for flags, what in HIT_PATHS:            # flags = 0 first: the closest hit of the timed kernel (k_render_tc)
+        idx, t, nrm = be.primary_hits(flags=flags)
+        assert_bits_equal(idx, oi, f"hit index ({what})")
+        rel_t = np.abs(t - ot) / np.maximum(np.abs(ot), 1e-30)
+        rel_n = np.abs(nrm - on) / np.maximum(np.abs(on), 1e-30)
+        assert rel_t.max() <= 1e-5 and rel_n.max() <= 1e-5, what     # the stated tolerance
+        assert_bits_equal(t, ot, f"t ({what})")                      # ... and in fact 0 ulp
+        assert_bits_equal(nrm, on, f"normal ({what})")
+        # tiles of the same pass
+        ti, tt, tn = be.primary_hits(tile=(37, 11, 501, 97), flags=flags)
+        assert_bits_equal(ti, oi[11:108, 37:538], f"tile hit index ({what})")
+        assert_bits_equal(tt, ot[11:108, 37:538], f"tile t ({what})")
 
 
 @pytest.mark.parametrize("n_side", [1, 5, 30, 46])
@@ -80,26 +95,34 @@ def test_closest_hits_arbitrary_rays(be, port, n_side):
     d = rng.normal(size=(n, 3)).astype(np.float32) * rng.choice(np.float32([1e-3, 1.0, 1.0, 50.0]), (n, 1))
     rays = np.concatenate([o, d], 1).astype(np.float32)
     be.upload_scene(sc)
-    gi, gt, gn = be.closest_hits(rays, flags=FLAG_EXACT | FLAG_BRUTE)
     oi, ot, on, _ = port.closest_hits(sc, rays)
-    assert_bits_equal(gi, oi, "index")
-    assert_bits_equal(gt, ot, "t")
-    assert_bits_equal(gn, on, "normal")
     assert (oi >= 0).mean() > .2
+    # parity kernels, and the throughput kernels' closest hit: all spheres (2), tensor filter (126, 901), FMA filter (2117)
+    for flags in (FLAG_EXACT | FLAG_BRUTE, FLAG_BRUTE, FLAG_BRUTE | FLAG_FILTER_FMA):
+        gi, gt, gn = be.closest_hits(rays, flags=flags)
+        assert_bits_equal(gi, oi, f"index (flags {flags})")
+        assert_bits_equal(gt, ot, f"t (flags {flags})")
+        assert_bits_equal(gn, on, f"normal (flags {flags})")
 
 
 # ------------------------------------------------------------------ full renders, exact mode: bit-exact
+@pytest.mark.parametrize("filt", [0, FLAG_FILTER_FMA], ids=["tensor-kernel", "parity-kernel"])
 @pytest.mark.parametrize("name,W,H,spp,depth", [("simple", 96, 54, 4, 50), ("huge", 96, 54, 3, 50),
                                                  ("huge", 33, 7, 2, 5), ("simple", 31, 17, 5, 1)])
-def test_exact_render_is_bit_identical_to_oracle(be, port, name, W, H, spp, depth):
+def test_exact_render_is_bit_identical_to_oracle(be, port, name, W, H, spp, depth, filt):
+    """RT_FLAG_EXACT: on the huge scene the dispatch takes the tensor-core kernel with parity shading
+    (k_render_tc<true>) -- the timed kernel's closest hit and loop structure -- or, with RT_FLAG_FILTER_FMA, the
+    straightforward parity kernel; both must reproduce the oracle's accumulators, statistics and 8-bit image exactly."""
     sc = scenes.get_scene(name, W, H)
     setup(be, sc, W, H)
-    be.render(spp, depth, seed=0xC0FFEE12345, flags=FLAG_EXACT)
+    be.render(spp, depth, seed=0xC0FFEE12345, flags=FLAG_EXACT | filt)
     acc = be.readback_accum()
     o = port.render(sc, W, H, spp, depth, 0xC0FFEE12345, nthreads=64, rng=RNG_PHILOX, want_fixed=True)
     assert_bits_equal(acc[..., :3], o["fixed"], "32.32 radiance sums")
     assert (acc[..., 3] == spp).all()
     st = be.stats()
+    want = "rtf::k_render_tc<true>" if (name == "huge" and not filt) else "rtx::k_render"
+    assert KERNEL_NAMES[st["last_kernel"]] == want
     assert st["samples"] == W * H * spp
     assert st["segments"] == int(o["stats"][0])
     assert st["sky"] == int(o["stats"][1])
@@ -228,6 +251,50 @@ def test_render_matches_reference_cpu_render_statistically(be, golden, name, fla
     assert abs((st["capped"] + st["absorbed"]) / st["samples"] - ref_cap) < 0.05 * ref_cap + 1e-4
 
 
+def mc_check_masked(mean_gpu, n_gpu, g, name, mask, what):
+    """The RMSE and luminance bounds of mc_check restricted to the pixels of `mask` (one material class)."""
+    ref_mean, var = g[f"{name}_mean"].astype(np.float64)[mask], g[f"{name}_var"].astype(np.float64)[mask]
+    n_ref = int(g[f"{name}_cfg"][2])
+    k = 1.0 / n_ref + 1.0 / n_gpu
+    diff = mean_gpu.astype(np.float64)[mask] - ref_mean                       # (npx, 3)
+    rmse, bound = np.sqrt((diff ** 2).mean()), 1.15 * np.sqrt(var.mean() * k)
+    assert rmse <= bound, f"{name}/{what}: RMSE {rmse:.5f} exceeds the noise bound {bound:.5f} on {mask.sum()} pixels"
+    wy = np.array([.2126, .7152, .0722])
+    dlum = abs((diff @ wy).mean())
+    sig = np.sqrt(((var * wy ** 2).sum(-1) * k).sum()) / diff.shape[0]
+    assert dlum <= 4 * sig, f"{name}/{what}: mean luminance differs by {dlum:.6f} > 4 sigma = {4 * sig:.6f}"
+    return rmse, bound, dlum, sig
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_EXACT], ids=["throughput-shading", "parity-shading"])
+@pytest.mark.parametrize("name", ["simple", "huge"])
+def test_render_matches_reference_cpu_render_at_baseline_geometry(be, golden, port, name, flags):
+    """SURVEY 8(c)(iii) at the size it asks for: the compiled reference rendered 640x360 (BASELINE's 1280x720 camera and
+    aspect, a quarter of the pixels) at 256 spp (huge) / 1024 spp (simple), depth 50 -- tests/golden/reference_render_640.npz,
+    ~2 700 core-seconds.  Whole-image bounds, then the same bounds PER MATERIAL CLASS of the primary hit (sky, lambert,
+    metal, glass), so that a bias confined to one material cannot hide in another's variance."""
+    g = golden("reference_render_640")
+    W, H, _, depth, _ = (int(x) for x in g[f"{name}_cfg"])
+    sc = scenes.get_scene(name, W, H)
+    setup(be, sc, W, H)
+    n_gpu = 2048
+    be.render(n_gpu, depth, seed=2718, flags=flags)
+    mean = be.readback_f32()
+    mc_check(mean, n_gpu, g, name)
+    st = be.stats()
+    ref_seg = float(g[f"{name}_stats"][0]) / (W * H * int(g[f"{name}_cfg"][2]))
+    assert abs(st["segments"] / st["samples"] - ref_seg) < 0.01 * ref_seg       # path-length statistics agree
+    idx, _, _ = port.primary_hits(sc.with_camera(aperture=0.0), W, H, nthreads=64)
+    kind = np.where(idx < 0, 3, sc.mat_kind[sc.sphere_mat[np.maximum(idx, 0)]])
+    checked = 0
+    for k, what in enumerate(("lambert", "metal", "dielectric", "sky")):
+        mask = kind == k
+        if mask.sum() >= 400:
+            mc_check_masked(mean, n_gpu, g, name, mask, what)
+            checked += 1
+    assert checked >= 3
+
+
 def test_fast_and_exact_builds_agree_statistically(be):
     W, H = 160, 90
     setup(be, scenes.huge_scene(W, H), W, H)
@@ -236,7 +303,7 @@ def test_fast_and_exact_builds_agree_statistically(be):
     be.clear()
     be.render(512, 50, seed=3, flags=0)
     b = be.readback_f32().astype(np.float64)
-    # same seeds and counters: almost every path is identical, a few diverge at grazing hits
+    # independent sample sets (the throughput shading draws the unit ball by inversion): agreement to Monte Carlo precision
     assert np.sqrt(((a - b) ** 2).mean()) < 0.01
     assert abs(a.mean() - b.mean()) < 1e-3
 
@@ -312,20 +379,22 @@ def test_tensor_filter_never_drops_a_hit(be, n):
     assert st["filter_misses"] == 0, "FMA-pipe filter dropped a hit"
 
 
-def test_tensor_and_fma_filters_render_the_same_image(be):
-    """Both throughput kernels trace the same counter-based paths; they differ only by how the compiler contracts
-    the shading arithmetic, so a few paths diverge at grazing hits and every pixel agrees to Monte Carlo precision."""
+def test_tensor_fma_and_lbvh_kernels_render_identical_accumulators(be):
+    """The three throughput kernels trace the same counter-based paths with the same closest hit (the IEEE reference
+    test decides in all of them) and the same shading code: identical accumulators and path statistics, bit for bit."""
     W, H = 160, 90
     setup(be, scenes.huge_scene(W, H), W, H)
-    be.render(512, 50, seed=3, flags=0)
-    a = be.readback_f32().astype(np.float64); sa = be.stats()
-    be.clear(); be.reset_stats()
-    be.render(512, 50, seed=3, flags=FLAG_FILTER_FMA)
-    b = be.readback_f32().astype(np.float64); sb = be.stats()
-    assert np.sqrt(((a - b) ** 2).mean()) < 0.01
-    assert abs(a.mean() - b.mean()) < 1e-3
-    assert abs(sa["segments"] - sb["segments"]) < 2e-3 * sb["segments"]
-    assert sa["samples"] == sb["samples"] == W * H * 512
+    out = {}
+    for flags, want in ((0, "rtf::k_render_tc<false>"), (FLAG_FILTER_FMA, "rtf::k_render"), (FLAG_LBVH, "rtf::k_render_bvh")):
+        be.clear(); be.reset_stats()
+        be.render(64, 50, seed=3, flags=flags)
+        out[flags] = (be.readback_accum().copy(), be.stats())
+        assert KERNEL_NAMES[out[flags][1]["last_kernel"]] == want
+        assert out[flags][1]["samples"] == W * H * 64
+    for flags in (FLAG_FILTER_FMA, FLAG_LBVH):
+        assert_bits_equal(out[flags][0], out[0][0], f"accumulators, flags {flags} vs tensor kernel")
+        for k in ("segments", "sky", "absorbed", "capped"):
+            assert out[flags][1][k] == out[0][1][k], k
 
 
 # ------------------------------------------------------------------ resolve + e2e call
@@ -511,12 +580,9 @@ def test_lbvh_equals_brute_force(be, n_side):
     for flags in (FLAG_EXACT, 0):
         bi, bt, bn = be.closest_hits(rays, flags=flags | FLAG_BRUTE)
         li, lt, ln = be.closest_hits(rays, flags=flags | FLAG_LBVH)
-        if flags == FLAG_EXACT:
-            assert_bits_equal(li, bi, "index")
-            assert_bits_equal(lt, bt, "t")
-            assert_bits_equal(ln, bn, "normal")
-        else:   # the throughput build's brute loop uses approximate sqrt / reciprocal in the candidate test
-            assert (li != bi).mean() < 1e-3
+        assert_bits_equal(li, bi, f"index (flags {flags})")
+        assert_bits_equal(lt, bt, f"t (flags {flags})")
+        assert_bits_equal(ln, bn, f"normal (flags {flags})")
     st = be.stats()
     assert st["node_visits"] > 0
 
@@ -586,10 +652,11 @@ def test_lbvh_thin_deep_tree_equals_brute_force(be):
     il, tl, nl = be.closest_hits(rays, flags=FLAG_EXACT | FLAG_LBVH)
     assert np.array_equal(ib, il)
     assert_bits_equal(tb, tl, "t")
-    # throughput build: the LBVH leaf test and the tensor kernel's candidate test round differently, so compare hits
-    ib, tb, nb = be.closest_hits(rays, flags=FLAG_BRUTE)
-    il, tl, nl = be.closest_hits(rays, flags=FLAG_LBVH)
-    assert np.array_equal(ib, il)
+    # throughput kernels: the LBVH leaves and the tensor kernel's candidates run the same IEEE test
+    ib2, tb2, nb2 = be.closest_hits(rays, flags=FLAG_BRUTE)
+    il2, tl2, nl2 = be.closest_hits(rays, flags=FLAG_LBVH)
+    assert np.array_equal(ib2, ib) and np.array_equal(il2, ib)
+    assert_bits_equal(tb2, tb, "t, tensor kernel"); assert_bits_equal(tl2, tb, "t, throughput LBVH")
     be.clear(); be.reset_stats(); be.render(6, 50, seed=4, flags=FLAG_LBVH)
     st = be.stats()
     assert st["samples"] == W * H * 6 and st["node_visits"] > 0

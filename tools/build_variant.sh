@@ -8,7 +8,7 @@ out="$HERE/build/variants/$name"; mkdir -p "$out"
 SRC="$HERE/raytracinginoneweekend_b200/csrc"
 COMMON="-std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-ffp-contract=off,-fvisibility=hidden $*"
 nvcc $COMMON --fmad=false -c $SRC/rt_kernels_exact.cu -o $out/exact.o &
-nvcc $COMMON --fmad=true -c $SRC/rt_kernels_fast.cu -o $out/fast.o -Xptxas -v 2> $out/fast.ptxas.log &
+nvcc $COMMON --fmad=false -c $SRC/rt_kernels_fast.cu -o $out/fast.o -Xptxas -v 2> $out/fast.ptxas.log &
 nvcc $COMMON -c $SRC/rt_common.cu -o $out/common.o &
 nvcc $COMMON -c $SRC/rt_lbvh.cu -o $out/lbvh.o &
 nvcc $COMMON -c $SRC/rt_api.cu -o $out/api.o &
