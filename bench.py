@@ -264,8 +264,11 @@ def run_gpu_arm(args):
     stream = torch.cuda.Stream(device=local)
     be.set_stream(stream.cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-    queue = None
-    if world > 1:
+    queue = dq = None
+    if world > 1 and args.mgpu == "device":
+        # device-side tile queue: cursors + frame in rank 0's memory, mapped by the other ranks through CUDA IPC
+        dq = multigpu.DeviceQueueFrame(be, rank, world, dist, torch, stream)
+    elif world > 1:
         qname = f"/rtiow_bench_{os.environ.get('MASTER_PORT', '0')}"
         if rank == 0:
             queue = TileQueue(qname, create=True)
@@ -284,7 +287,9 @@ def run_gpu_arm(args):
         be.framebuffer(W, H)
         tiles = multigpu.interleave_tiles(multigpu.make_tiles(W, H, TILE_W, TILE_H), world)
         sched = renderer = None
-        if world > 1:
+        if dq is not None:
+            dq.map_frame()
+        elif world > 1:
             sched = multigpu.StealingScheduler(queue, rank, world, len(tiles))
             renderer = multigpu.CudaTileRenderer(be, TILE_W, TILE_H, spp, DEPTH, SEED, flags)
         r_start = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
@@ -293,6 +298,13 @@ def run_gpu_arm(args):
         def step(i=None):
             """clear -> render (all samples) -> resolve -> (N>1) gather on rank 0; all ordered on `stream`.
             r_start/r_end bracket the render phase as ONE interval (overlapped chunk launches are not summed)."""
+            if dq is not None:                # ONE persistent launch per GPU: tiles pulled from the device-side queue,
+                if i is not None:             # texels stored into rank 0's frame, NCCL all-reduce as the acknowledgement
+                    r_start[i].record(stream)
+                dq.render_frame(tiles, TILE_W, TILE_H, spp, DEPTH, SEED, flags)
+                if i is not None:
+                    r_end[i].record(stream)
+                return
             be.clear()
             if i is not None:
                 r_start[i].record(stream)
@@ -331,8 +343,10 @@ def run_gpu_arm(args):
         barrier()
         wall = time.perf_counter() - t_wall0
         dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-        render_ms = sum(s.elapsed_time(e) for s, e in zip(r_start, r_end))
         st = be.stats()
+        # render phase of this rank per step: the kernel's own event pair when a step is one launch; the interval around
+        # the chunk sequence when the host schedules overlapped chunks (their event pairs overlap and must not be summed)
+        render_ms = st["render_ms"] if (world == 1 or dq is not None) else sum(s.elapsed_time(e) for s, e in zip(r_start, r_end))
 
         frame_hash = None
         if want_hash and rank == 0:               # rank 0's device frame after the last step (gathered when N > 1)
@@ -373,7 +387,8 @@ def run_gpu_arm(args):
         t = torch.tensor([dev_ms, e2e["ms"] if e2e else 0.0, wall, render_ms], dtype=torch.float64, device=dev)
         work = torch.tensor([st["samples"], st["segments"], st["launches"], st["node_visits"], st["sphere_tests"]],
                             dtype=torch.float64, device=dev)
-        mine = torch.tensor([dev_ms, render_ms, float(sched.own_taken if sched else 0), float(sched.stolen if sched else 0)],
+        own_tiles = be.tiles_rendered() if dq is not None else (sched.own_taken if sched else 0)
+        mine = torch.tensor([dev_ms, render_ms, float(own_tiles), float(sched.stolen if sched else 0)],
                             dtype=torch.float64, device=dev)
         per_rank = [torch.zeros_like(mine) for _ in range(world)] if world > 1 else [mine]
         if world > 1:
@@ -391,12 +406,13 @@ def run_gpu_arm(args):
             "sphere_tests": sphere_tests, "stats_rank0": st, "kernel": KERNEL_NAMES.get(st["last_kernel"], "?"),
             "frame_sha256": frame_hash,
             "ranks": [{"rank": i, "step_ms": float(v[0]) / steps, "render_phase_ms": float(v[1]) / steps,
-                       "own_tiles_last_step": int(v[2]), "stolen_tiles_last_step": int(v[3])} for i, v in enumerate(per_rank)],
+                       "tiles_last_step": int(v[2]), "stolen_tiles_last_step": int(v[3])} for i, v in enumerate(per_rank)],
         }
         if e2e:
             res["e2e"] = {"value": float(W) * H * spp * e2e["steps"] / (e2e_ms * 1e-3) / 1e9, "unit": UNIT,
                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"], "steps": e2e["steps"],
                           "call": "rt_render_frame (cuda_impl-shaped: host scene in, host RGB8 out)" if world == 1
+                                  else "rt_scene_upload + rt_render_queue + rt_resolve_tiles_to(rank 0) + NCCL ack + D2H on rank 0" if dq is not None
                                   else "rt_scene_upload + tile-stolen rt_render_tiles + NCCL reduce + D2H on rank 0"}
         return res
 
@@ -497,7 +513,10 @@ def run_gpu_arm(args):
             "dtype": "f32", "data": "synthetic",
             "config": workload_config(wname, WORKLOADS[wname][0], sc.n, head["W"], head["H"], head["spp"]),
             "impl_detail": {"accel": accel, "kernel": head["kernel"],
-                            "parallelism": f"tile-sharded x{world}, stealing, NCCL reduce to rank 0" if world > 1 else "1 GPU",
+                            "parallelism": ("1 GPU" if world == 1 else
+                                            f"x{world}: device-side tile queue (cursors in rank 0's memory over NVLink, in-kernel stealing), "
+                                            "one persistent launch per GPU and frame, resolve stores into rank 0's frame (CUDA IPC), NCCL all-reduce ack"
+                                            if dq is not None else f"tile-sharded x{world}, host-scheduled stealing, NCCL reduce to rank 0"),
                             "l2": "flushed between timed steps (256 MiB write)",
                             "segments_per_sample": head["segments"] / max(1.0, head["samples"]),
                             "closest_hit": "bit-identical to the oracle (index, t, normal) in every kernel; shading of the timed "
@@ -550,6 +569,9 @@ def run_gpu_arm(args):
         except Exception as exc:  # the checker is optional for the number, never for the product
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": cpu_threads(), "kind": "port", "sample": f"failed: {exc}"}
 
+    if dq is not None:
+        barrier()
+        dq.close()
     if queue is not None:
         barrier()
         queue.close()
@@ -603,6 +625,8 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override spp (debug only; invalidates the headline number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="headline workload only (profiling runs)")
+    ap.add_argument("--mgpu", choices=["device", "host"], default="device",
+                    help="N > 1: device-side tile queue + peer-store gather (default) | host-scheduled chunks + NCCL reduce (round 1)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         print(f"bench.py: warning: --warmup {args.warmup} < 3 breaks the timing rules", file=sys.stderr)

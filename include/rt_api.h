@@ -77,7 +77,9 @@ enum {
                                      filled by the next).  The caller promises disjoint tiles within a frame, as the multi-GPU
                                      tile scheduler does; every other call on the context is ordered after all of them. */
 };
-#define RT_BRUTE_MAX_SPHERES 8192u
+#define RT_BRUTE_MAX_SPHERES 8192u   /* parity kernels; the throughput kernel with the FMA-chain filter fits about 5 800 spheres in
+                                        shared memory -- beyond that RT_FLAG_ACCEL_BRUTE fails with a clear message and the
+                                        automatic choice is the LBVH (which it already is above RT_AUTO_LBVH_SPHERES) */
 #define RT_AUTO_LBVH_SPHERES 768u
 
 typedef struct rt_ctx rt_ctx;
@@ -136,6 +138,7 @@ RT_EXPORT int rt_destroy(rt_ctx *ctx);
 
 /* Use an existing CUDA stream (e.g. torch's current stream); NULL restores the ctx's own stream. */
 RT_EXPORT int rt_set_stream(rt_ctx *ctx, void *cuda_stream);
+RT_EXPORT int rt_get_stream(rt_ctx *ctx, void **cuda_stream);   /* the stream the context currently queues its work on */
 RT_EXPORT int rt_sync(rt_ctx *ctx);
 /* Block until at most `max_in_flight` rt_render / rt_render_tiles calls are still running. */
 RT_EXPORT int rt_throttle(rt_ctx *ctx, uint32_t max_in_flight);
@@ -244,6 +247,56 @@ RT_EXPORT int rt_queue_open(rt_queue **out, const char *name, int create);
 RT_EXPORT int rt_queue_reset(rt_queue *q, uint32_t slot, uint64_t value);
 RT_EXPORT int rt_queue_next(rt_queue *q, uint32_t slot, uint64_t n, uint64_t *previous);
 RT_EXPORT int rt_queue_close(rt_queue *q, int unlink_name);
+
+/* ---- device-side tile queue (multi-GPU) ---------------------------------------------------------
+ * The frame's tile list (interleaved so that every range sees the image's cost mix) is split into one contiguous range
+ * per rank.  The cursors of all ranges live in ONE device allocation in rank 0's memory, reachable from the other GPUs
+ * over NVLink (peer access in one process -- rt_multi below -- or CUDA IPC between processes).  rt_render_queue is ONE
+ * persistent launch per GPU and frame: the kernel itself takes tiles from its own range (a system-scope atomicAdd on
+ * the cursor) and, when that is dry, steals from the other ranges -- no host round trip, no per-chunk launch.
+ * rt_resolve_tiles_to then resolves exactly the tiles this GPU rendered and stores the texels straight into rank 0's
+ * frame (peer-mapped): that store IS the framebuffer gather.
+ *   rank 0:  rt_queue_dev_create -> (rt_ipc_export) ; per frame rt_queue_dev_reset, then a barrier
+ *   rank r:  (rt_ipc_import) ; per frame rt_render_queue + rt_resolve_tiles_to(rank 0's rgb8) ; then a barrier / ack
+ * tile_w * tile_h must be a multiple of 256. */
+#define RT_IPC_HANDLE_BYTES 64
+RT_EXPORT int rt_queue_dev_create(rt_ctx *ctx, void **cursors_dev);
+RT_EXPORT int rt_queue_dev_reset(rt_ctx *ctx, void *cursors_dev, uint32_t ntiles, uint32_t nranks);  /* on the ctx stream */
+RT_EXPORT int rt_queue_dev_free(rt_ctx *ctx, void *cursors_dev);
+RT_EXPORT int rt_render_queue(rt_ctx *ctx, const rt_tile *tiles, uint32_t ntiles, uint32_t tile_w, uint32_t tile_h,
+                              const rt_render_params *params, void *cursors_dev, uint32_t rank, uint32_t nranks);
+/* rgb8_frame_dev: device pointer to a W*H*3 frame (rank 0's, peer-mapped), or NULL for this context's own RGB8 buffer */
+RT_EXPORT int rt_resolve_tiles_to(rt_ctx *ctx, void *rgb8_frame_dev);
+RT_EXPORT int rt_queue_tiles_rendered(rt_ctx *ctx, uint32_t *count);   /* tiles the last rt_render_queue launch acquired */
+/* copy the context's device RGB8 buffer to the HOST as it is (no resolve): rank 0 after the peers' stores */
+RT_EXPORT int rt_copy_rgb8(rt_ctx *ctx, uint8_t *dst);
+/* CUDA IPC plumbing for one process per GPU: export a device allocation of this context (the cursors, the RGB8 frame
+ * from rt_device_rgb8), import it in another process; handles are RT_IPC_HANDLE_BYTES opaque bytes. */
+RT_EXPORT int rt_ipc_export(rt_ctx *ctx, void *devptr, unsigned char handle[RT_IPC_HANDLE_BYTES]);
+RT_EXPORT int rt_ipc_import(rt_ctx *ctx, const unsigned char handle[RT_IPC_HANDLE_BYTES], void **devptr);
+RT_EXPORT int rt_ipc_close(rt_ctx *ctx, void *devptr);
+
+/* ---- several GPUs behind ONE host call (rt_create(devices, ndev); host code stays C++) --------------
+ * One process, one context + stream + host worker thread per GPU, peer access to devices[0], the device-side tile
+ * queue above, resolve stores into devices[0]'s frame; NCCL (ncclCommInitAll, loaded at run time) provides the
+ * end-of-frame acknowledgement and, with RT_MULTI_GATHER_NCCL or when peer access is unavailable, the gather itself
+ * (ncclReduce(SUM, uint8) of the per-GPU frames, whose foreign tiles are zero).
+ * rt_multi_render_frame is cuda_impl(width, height, texels) on N GPUs: host scene in, host RGB8 out; the N-GPU frame
+ * is bit-identical to the 1-GPU frame (integer accumulation, (pixel, sample)-keyed RNG). */
+typedef struct rt_multi rt_multi;
+enum { RT_MULTI_GATHER_NCCL = 1u << 0 };   /* rt_multi_render_frame gather_flags */
+RT_EXPORT int rt_multi_create(rt_multi **out, const int *devices, int ndev);
+RT_EXPORT int rt_multi_destroy(rt_multi *m);
+RT_EXPORT int rt_multi_device_count(rt_multi *m);
+RT_EXPORT rt_ctx *rt_multi_ctx(rt_multi *m, int i);          /* context of devices[i] (statistics, probes) */
+RT_EXPORT int rt_multi_render_frame(rt_multi *m, const rt_sphere *spheres, uint32_t n, const rt_material *materials,
+                                    uint32_t nmat, const float camera13[13], uint32_t width, uint32_t height,
+                                    const rt_render_params *params, uint32_t tile_w, uint32_t tile_h,
+                                    uint32_t gather_flags, uint8_t *rgb8_out);
+/* the same without re-uploading the scene (rt_multi_render_frame must have run once): device-timed benchmarking */
+RT_EXPORT int rt_multi_render_again(rt_multi *m, const rt_render_params *params, uint32_t gather_flags, uint8_t *rgb8_out);
+/* out = {tiles rendered by device i in the last frame} for i < ndev; NCCL in use (0/1) in nccl_used */
+RT_EXPORT int rt_multi_last_frame(rt_multi *m, uint32_t *tiles_per_device, int *nccl_used, double *frame_ms);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,10 @@ EXPORTS = [
     "rt_device_accum", "rt_device_rgb8", "rt_resolve_device", "rt_render_frame", "rt_stats_get",
     "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info", "rt_debug_sample_ball", "rt_render_progressive",
     "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
+    "rt_get_stream", "rt_queue_dev_create", "rt_queue_dev_reset", "rt_queue_dev_free", "rt_render_queue",
+    "rt_resolve_tiles_to", "rt_queue_tiles_rendered", "rt_copy_rgb8", "rt_ipc_export", "rt_ipc_import", "rt_ipc_close",
+    "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_ctx", "rt_multi_render_frame",
+    "rt_multi_render_again", "rt_multi_last_frame",
 ]
 
 
@@ -124,10 +128,29 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_queue_reset.argtypes = [vp, u32, u64]
     lib.rt_queue_next.argtypes = [vp, u32, u64, C.POINTER(u64)]
     lib.rt_queue_close.argtypes = [vp, i32]
+    lib.rt_get_stream.argtypes = [vp, C.POINTER(vp)]
+    lib.rt_queue_dev_create.argtypes = [vp, C.POINTER(vp)]
+    lib.rt_queue_dev_reset.argtypes = [vp, vp, u32, u32]
+    lib.rt_queue_dev_free.argtypes = [vp, vp]
+    lib.rt_render_queue.argtypes = [vp, vp, u32, u32, u32, C.POINTER(RtRenderParams), vp, u32, u32]
+    lib.rt_resolve_tiles_to.argtypes = [vp, vp]
+    lib.rt_queue_tiles_rendered.argtypes = [vp, C.POINTER(u32)]
+    lib.rt_copy_rgb8.argtypes = [vp, vp]
+    lib.rt_ipc_export.argtypes = [vp, vp, vp]
+    lib.rt_ipc_import.argtypes = [vp, vp, C.POINTER(vp)]
+    lib.rt_ipc_close.argtypes = [vp, vp]
+    lib.rt_multi_create.argtypes = [C.POINTER(vp), C.POINTER(i32), i32]
+    lib.rt_multi_destroy.argtypes = [vp]
+    lib.rt_multi_device_count.argtypes = [vp]
+    lib.rt_multi_ctx.argtypes = [vp, i32]
+    lib.rt_multi_render_frame.argtypes = [vp, vp, u32, vp, u32, fp, u32, u32, C.POINTER(RtRenderParams), u32, u32, u32, vp]
+    lib.rt_multi_render_again.argtypes = [vp, C.POINTER(RtRenderParams), u32, vp]
+    lib.rt_multi_last_frame.argtypes = [vp, C.POINTER(u32), C.POINTER(i32), C.POINTER(C.c_double)]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("rt_last_error", "rt_version"):
+        if name not in ("rt_last_error", "rt_version", "rt_multi_ctx"):
             fn.restype = C.c_int
+    lib.rt_multi_ctx.restype = vp
     _lib = lib
     return lib
 
@@ -216,6 +239,59 @@ class Backend:
         tiles = np.ascontiguousarray(tiles, np.uint32).reshape(-1, 4)
         p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
         _check(self.lib, self.lib.rt_render_tiles(self.ctx, tiles.ctypes.data, tiles.shape[0], int(tile_w), int(tile_h), C.byref(p)))
+
+    # ---- device-side tile queue (multi-GPU) ---------------------------------
+    def get_stream(self):
+        p = C.c_void_p()
+        _check(self.lib, self.lib.rt_get_stream(self.ctx, C.byref(p)))
+        return p.value
+
+    def queue_dev_create(self):
+        """Range cursors of the device-side tile queue, allocated on THIS context's device (rank 0); -> device pointer."""
+        p = C.c_void_p()
+        _check(self.lib, self.lib.rt_queue_dev_create(self.ctx, C.byref(p)))
+        return p.value
+
+    def queue_dev_reset(self, cursors, ntiles, nranks):
+        _check(self.lib, self.lib.rt_queue_dev_reset(self.ctx, C.c_void_p(cursors), int(ntiles), int(nranks)))
+
+    def queue_dev_free(self, cursors):
+        _check(self.lib, self.lib.rt_queue_dev_free(self.ctx, C.c_void_p(cursors)))
+
+    def render_queue(self, tiles, tile_w, tile_h, cursors, rank, nranks, spp, max_depth=50, seed=1, sample_base=0, flags=0):
+        """ONE persistent launch that pulls its tiles from the device-side queue (own range first, then stealing)."""
+        tiles = np.ascontiguousarray(tiles, np.uint32).reshape(-1, 4)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), int(sample_base), int(flags))
+        _check(self.lib, self.lib.rt_render_queue(self.ctx, tiles.ctypes.data, tiles.shape[0], int(tile_w), int(tile_h), C.byref(p),
+                                                   C.c_void_p(cursors), int(rank), int(nranks)))
+
+    def resolve_tiles_to(self, rgb8_frame_dev=None):
+        """Resolve the tiles the last render_queue launch rendered into a device RGB8 frame (None: this context's own)."""
+        _check(self.lib, self.lib.rt_resolve_tiles_to(self.ctx, C.c_void_p(rgb8_frame_dev) if rgb8_frame_dev else None))
+
+    def tiles_rendered(self):
+        n = C.c_uint32(0)
+        _check(self.lib, self.lib.rt_queue_tiles_rendered(self.ctx, C.byref(n)))
+        return int(n.value)
+
+    def copy_rgb8(self):
+        out = np.zeros((self.H, self.W, 3), np.uint8)
+        _check(self.lib, self.lib.rt_copy_rgb8(self.ctx, out.ctypes.data))
+        return out
+
+    def ipc_export(self, devptr) -> bytes:
+        h = (C.c_ubyte * 64)()
+        _check(self.lib, self.lib.rt_ipc_export(self.ctx, C.c_void_p(devptr), h))
+        return bytes(h)
+
+    def ipc_import(self, handle: bytes):
+        h = (C.c_ubyte * 64).from_buffer_copy(handle)
+        p = C.c_void_p()
+        _check(self.lib, self.lib.rt_ipc_import(self.ctx, h, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, devptr):
+        _check(self.lib, self.lib.rt_ipc_close(self.ctx, C.c_void_p(devptr)))
 
     def primary_hits(self, tile=None, flags=FLAG_EXACT):
         x0, y0, w, h = tile if tile is not None else (0, 0, self.W, self.H)
@@ -330,6 +406,69 @@ class Backend:
         out = (C.c_double * 3)()
         _check(self.lib, self.lib.rt_fp32_peak_probe(self.ctx, out))
         return dict(tflops=out[0], ms=out[1], sm_count=int(out[2]))
+
+
+class _CtxView(Backend):
+    """A Backend face on a context owned by an rt_multi (never destroyed from here)."""
+
+    def __init__(self, lib, ctx, device, W, H):
+        self.lib, self.ctx, self.device, self.W, self.H = lib, ctx, device, W, H
+
+    def close(self):
+        self.ctx = None
+
+
+class MultiBackend:
+    """rt_multi: several GPUs of ONE process behind one call (device-side tile queue, peer-store gather, NCCL ack)."""
+    GATHER_NCCL = 1
+
+    def __init__(self, devices):
+        self.lib = load_library()
+        self.devices = [int(d) for d in devices]
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        self.m = C.c_void_p()
+        _check(self.lib, self.lib.rt_multi_create(C.byref(self.m), arr, len(self.devices)))
+        self.W = self.H = 0
+
+    def close(self):
+        if getattr(self, "m", None):
+            self.lib.rt_multi_destroy(self.m)
+            self.m = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def ctx(self, i):
+        return _CtxView(self.lib, C.c_void_p(self.lib.rt_multi_ctx(self.m, int(i))), self.devices[i], self.W, self.H)
+
+    def render_frame(self, scene, W, H, spp, max_depth=50, seed=1, flags=0, tile_w=128, tile_h=64, gather=0, out=None, packed=None):
+        sph, mat = packed if packed is not None else pack_scene(scene)
+        cam = np.ascontiguousarray(scene.camera, np.float32)
+        if out is None:
+            out = np.zeros((H, W, 3), np.uint8)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), 0, int(flags))
+        _check(self.lib, self.lib.rt_multi_render_frame(self.m, sph.ctypes.data, sph.shape[0], mat.ctypes.data, mat.shape[0],
+                                                         cam.ctypes.data_as(C.POINTER(C.c_float)), int(W), int(H), C.byref(p),
+                                                         int(tile_w), int(tile_h), int(gather), out.ctypes.data))
+        self.W, self.H = int(W), int(H)
+        return out
+
+    def render_again(self, spp, max_depth=50, seed=1, flags=0, gather=0, out=None, want_image=True):
+        if out is None and want_image:
+            out = np.zeros((self.H, self.W, 3), np.uint8)
+        p = RtRenderParams(int(spp), int(max_depth), int(seed), 0, int(flags))
+        _check(self.lib, self.lib.rt_multi_render_again(self.m, C.byref(p), int(gather), out.ctypes.data if out is not None else None))
+        return out
+
+    def last_frame(self):
+        n = len(self.devices)
+        tiles = (C.c_uint32 * n)()
+        nccl, ms = C.c_int(0), C.c_double(0)
+        _check(self.lib, self.lib.rt_multi_last_frame(self.m, tiles, C.byref(nccl), C.byref(ms)))
+        return {"tiles_per_device": list(tiles), "nccl": bool(nccl.value), "frame_ms": ms.value}
 
 
 def write_ppm(path, rgb8):

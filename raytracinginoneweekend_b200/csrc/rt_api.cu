@@ -81,6 +81,9 @@ struct rt_ctx {
     float *d_scratch = nullptr;
 
     void *h_pin = nullptr; size_t h_pin_bytes = 0;   // pinned staging for uploads / readbacks
+    // device-side tile queue (rt_render_queue): the feed of the most recent launch and what its resolve needs
+    RtTileFeed *d_feed = nullptr; uint32_t feed_slots = 0;
+    const uint4 *feed_tiles = nullptr; uint32_t feed_TP = 0; bool feed_valid = false;
     void *d_hits = nullptr; size_t d_hits_bytes = 0; // grow-only scratch of rt_primary_hits / rt_closest_hits (index, t, normal, rays)
 
     // RT_FLAG_OVERLAP: chunk launches rotate over kAux auxiliary streams so that the tail of one persistent launch is
@@ -214,6 +217,18 @@ int pick_accel(rt_ctx *c, uint32_t flags, bool *lbvh)
         want_bvh = c->n > ((flags & RT_FLAG_EXACT) ? RT_BRUTE_MAX_SPHERES : RT_AUTO_LBVH_SPHERES);
     if (!want_bvh && c->n > RT_BRUTE_MAX_SPHERES)
         return fail(RT_ERR_INVALID, "brute force supports at most RT_BRUTE_MAX_SPHERES spheres (shared-memory staging)");
+    if (!want_bvh) {
+        // the brute-force kernels stage the scene in shared memory: the parity kernels take RT_BRUTE_MAX_SPHERES, the
+        // throughput kernel with the FMA-chain filter (sphere + filter records + its mask words) about 5.8 K spheres
+        const bool exact = (flags & RT_FLAG_EXACT) != 0;
+        const bool tensor = c->d_tcb && c->n >= RT_TC_MIN_SPHERES && !(flags & RT_FLAG_FILTER_FMA);
+        if (!tensor && rt_render_smem_bytes(c->npad, c->nfilt, exact, false) > RT_TC_SMEM_LIMIT) {
+            if (want_brute)
+                return fail(RT_ERR_INVALID, "brute force: the scene does not fit in shared memory for this build "
+                                            "(throughput build: about 5 800 spheres; RT_FLAG_EXACT: RT_BRUTE_MAX_SPHERES); use the LBVH");
+            want_bvh = true;
+        }
+    }
     if (want_bvh && c->n < 2) return fail(RT_ERR_INVALID, "the LBVH needs at least 2 spheres");
     if (want_bvh && !c->bvh_valid) {
         if (!c->bvh) { int r = rt_lbvh_create(&c->bvh); if (r) return fail(RT_ERR_CUDA, "rt_lbvh_create failed"); }
@@ -246,6 +261,9 @@ int occupancy(rt_ctx *c, bool exact, bool lbvh, size_t smem, int *ctas)
 }  // namespace
 
 extern "C" {
+
+// rt_multi.cu reports through the same thread-local error string
+int rt_internal_set_error(int code, const char *msg) { return fail(code, msg ? msg : ""); }
 
 const char *rt_last_error(void) { return g_err.c_str(); }
 const char *rt_version(void) { return "rtiow-b200 0.1 (sm_100a)"; }
@@ -297,7 +315,7 @@ int rt_destroy(rt_ctx *c)
     if (c->bvh) rt_lbvh_destroy(c->bvh);
     cudaFree(c->d_counter); cudaFree(c->d_tile_ring); cudaFree(c->d_stats); cudaFree(c->d_scratch);
     if (c->h_pin) cudaFreeHost(c->h_pin);
-    cudaFree(c->d_hits);
+    cudaFree(c->d_hits); cudaFree(c->d_feed);
     for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto &p : c->free_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -311,6 +329,13 @@ int rt_set_stream(rt_ctx *c, void *cuda_stream)
     CK(enter_ctx(c));
     CK(cudaStreamSynchronize(c->stream));
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return RT_OK;
+}
+
+int rt_get_stream(rt_ctx *c, void **cuda_stream)
+{
+    if (!c || !cuda_stream) return fail(RT_ERR_INVALID, "rt_get_stream: NULL argument");
+    *cuda_stream = (void *)c->stream;
     return RT_OK;
 }
 
@@ -540,9 +565,12 @@ int rt_clear(rt_ctx *c)
     return RT_OK;
 }
 
+// rt_render_queue: the launch pulls its tiles from the device-side queue instead of rendering the whole list
+struct QueueMode { uint32_t *cursors; uint32_t rank, nranks; };
+
 // Common scheduling of one or more launches over a tile list.  `tiles` all fit in tw x th pixel slots.
 static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, uint32_t tw, uint32_t th,
-                             const rt_render_params *p)
+                             const rt_render_params *p, const QueueMode *qm = nullptr)
 {
     if (!c->d_sph) return fail(RT_ERR_INVALID, "rt_render: no scene uploaded");
     if (!c->have_cam) return fail(RT_ERR_INVALID, "rt_render: no camera set");
@@ -558,9 +586,20 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     }
     const unsigned long long TP = (unsigned long long)tw * th;
     if (TP * p->spp >= (1ull << 31)) return fail(RT_ERR_INVALID, "rt_render: tile_pixels * spp must stay below 2^31; use smaller tiles or split spp with sample_base");
-    const bool overlap = (p->flags & RT_FLAG_OVERLAP) != 0;
+    const bool overlap = !qm && (p->flags & RT_FLAG_OVERLAP) != 0;
     if (overlap) CK(cudaSetDevice(c->device));        // no join: this launch may run beside the chunks already queued
     else CK(enter_ctx(c));
+    if (qm) {
+        if (TP % RT_BATCH != 0) return fail(RT_ERR_INVALID, "rt_render_queue: tile_w * tile_h must be a multiple of 256 (one work batch never straddles two tiles)");
+        if (ntiles > kTileRing) return fail(RT_ERR_INVALID, "rt_render_queue: too many tiles");
+        const uint32_t want = ntiles + 4096u;         // tiles this GPU can acquire + the dry slots its warps touch at the end
+        if (want > c->feed_slots) {
+            CK(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_feed); c->d_feed = nullptr; c->feed_slots = 0;
+            CK(cudaMalloc((void **)&c->d_feed, sizeof(RtTileFeed) + (size_t)want * sizeof(uint32_t)));
+            c->feed_slots = want;
+        }
+    }
 
     const bool exact = (p->flags & RT_FLAG_EXACT) != 0;
     bool lbvh = false;
@@ -607,7 +646,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     uint4 *d_tiles = nullptr;
     uint4 tile0 = make_uint4(tiles[0].x0, tiles[0].y0, tiles[0].w, tiles[0].h);
     bool tiles_from_pool = false;
-    if (ntiles > 1) {
+    if (ntiles > 1 || qm) {
         static_assert(sizeof(rt_tile) == sizeof(uint4), "rt_tile must be 16 bytes");
         if (ntiles <= kTileRing) {
             // (without RT_FLAG_OVERLAP everything is on one stream and a wrapped slice is only rewritten behind its readers)
@@ -621,8 +660,13 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         // pageable source: the runtime stages the bytes before returning, so `tiles` may be reused by the caller
         CK(cudaMemcpyAsync(d_tiles, tiles, (size_t)ntiles * sizeof(uint4), cudaMemcpyHostToDevice, st));
     }
-    CK(rt_launch_add_count(c->d_accum, c->W, tile0, d_tiles, ntiles, (uint32_t)TP, p->spp, st));
-    c->hs.launches += 1;
+    if (qm) {                                         // fresh feed: item counter 0, every slot RT_FEED_EMPTY
+        CK(cudaMemsetAsync(c->d_feed, 0, sizeof(RtTileFeed), st));
+        CK(cudaMemsetAsync(c->d_feed->slot, 0xff, (size_t)c->feed_slots * sizeof(uint32_t), st));
+    } else {
+        CK(rt_launch_add_count(c->d_accum, c->W, tile0, d_tiles, ntiles, (uint32_t)TP, p->spp, st));
+        c->hs.launches += 1;
+    }
 
     RtRenderArgs a{};
     a.sc = device_scene(c, lbvh);
@@ -641,14 +685,19 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.check = (p->flags & RT_FLAG_FILTER_CHECK) ? 1u : 0u;
     a.book = (p->flags & RT_FLAG_BOOK_OPTICS) ? 1u : 0u;
     a.smem_mats = smem_mats ? 1u : 0u;
+    if (qm) {
+        a.feed = c->d_feed; a.feed_slots = c->feed_slots;
+        a.q_cursors = qm->cursors; a.q_rank = qm->rank; a.q_nranks = qm->nranks; a.q_ntiles = ntiles;
+    }
 
-    // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic)
-    uint32_t per_band = (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);
+    // bands of consecutive tiles so that items = nt * TP * spp stays below 2^31 (32-bit item arithmetic);
+    // queue mode: ONE launch, the items are tile-relative and the feed's counter is 64 bits wide
+    uint32_t per_band = qm ? ntiles : (uint32_t)((((1ull << 31) - 1) / p->spp) / TP);
     for (uint32_t t0 = 0; t0 < ntiles; t0 += per_band) {
         uint32_t nt = (ntiles - t0 < per_band) ? (ntiles - t0) : per_band;
         a.t0 = t0;
         a.P = nt * (uint32_t)TP;
-        a.total_items = a.P * p->spp;
+        a.total_items = qm ? 0x7fffffffu : a.P * p->spp;
         if (c->counter_slot == kCounterRing) {
             CK(cudaMemsetAsync(c->d_counter, 0, kCounterRing * sizeof(uint32_t), st));
             c->counter_slot = 0;
@@ -656,12 +705,12 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         a.work_counter = c->d_counter + c->counter_slot++;
         const unsigned long long per_cta = tensor ? (unsigned long long)(RT_TC_WGS * 128)
                                            : small ? (unsigned long long)RT_THREADS : (unsigned long long)RT_THREADS * RT_RPT;
-        unsigned long long want_ctas = (a.total_items + per_cta - 1) / per_cta;
+        unsigned long long want_ctas = qm ? ~0ull : (a.total_items + per_cta - 1) / per_cta;
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
         cudaError_t e = small ? rtf::launch_render_small(a, grid, st)
-                        : tensor ? rtf::launch_render_tc(a, grid, smem, st, exact)
+                        : tensor ? (exact ? rtx::launch_render_tc(a, grid, smem, st) : rtf::launch_render_tc(a, grid, smem, st))
                         : exact ? rtx::launch_render(a, grid, smem, st, lbvh)
                                 : rtf::launch_render(a, grid, smem, st, lbvh);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
@@ -672,6 +721,11 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
                                    : (exact ? RT_KERNEL_RENDER_PARITY : RT_KERNEL_RENDER_FMA);
     }
     if (tiles_from_pool) CK(cudaFreeAsync(d_tiles, st));
+    if (qm) {                                         // the sample count of the tiles this GPU ended up rendering
+        CK(rt_launch_add_count_feed(c->d_accum, c->W, d_tiles, c->d_feed->slot, c->feed_slots, (uint32_t)TP, p->spp, st));
+        c->hs.launches += 1;
+        c->feed_tiles = d_tiles; c->feed_TP = (uint32_t)TP; c->feed_valid = true;
+    }
     CK(cudaEventRecord(ev.b, st));
     if (aux_slot >= 0) { CK(cudaEventRecord(c->aux_tail[aux_slot], st)); c->aux_dirty[aux_slot] = true; }
     c->pending.push_back(ev);
@@ -944,6 +998,111 @@ int rt_render_progressive(rt_ctx *c, const rt_render_params *p, uint32_t spp_per
     if (rc == RT_OK && cb && !stop && rgb8_out) cb(user, pass, done, rgb8_out);   // the final image also goes through the callback
     cleanup();
     return rc;
+}
+
+// ---------------------------------------------------------------- device-side tile queue (multi-GPU)
+int rt_queue_dev_create(rt_ctx *c, void **cursors)
+{
+    if (!c || !cursors) return fail(RT_ERR_INVALID, "rt_queue_dev_create: NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaMalloc(cursors, (size_t)RT_QUEUE_SLOTS * RT_QUEUE_STRIDE * sizeof(uint32_t)));
+    CK(cudaMemset(*cursors, 0, (size_t)RT_QUEUE_SLOTS * RT_QUEUE_STRIDE * sizeof(uint32_t)));
+    return RT_OK;
+}
+
+int rt_queue_dev_reset(rt_ctx *c, void *cursors, uint32_t ntiles, uint32_t nranks)
+{
+    if (!c || !cursors || nranks == 0 || nranks > RT_QUEUE_SLOTS) return fail(RT_ERR_INVALID, "rt_queue_dev_reset: bad argument");
+    CK(enter_ctx(c));
+    CK(rt_launch_queue_reset((uint32_t *)cursors, ntiles, nranks, c->stream));
+    c->hs.launches += 1;
+    return RT_OK;
+}
+
+int rt_queue_dev_free(rt_ctx *c, void *cursors)
+{
+    if (!c) return fail(RT_ERR_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaFree(cursors));
+    return RT_OK;
+}
+
+int rt_render_queue(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, uint32_t tile_w, uint32_t tile_h,
+                    const rt_render_params *p, void *cursors, uint32_t rank, uint32_t nranks)
+{
+    if (!c || !p || !tiles || !cursors) return fail(RT_ERR_INVALID, "rt_render_queue: NULL argument");
+    if (ntiles == 0 || nranks == 0 || rank >= nranks || nranks > RT_QUEUE_SLOTS)
+        return fail(RT_ERR_INVALID, "rt_render_queue: bad tile count, rank or rank count");
+    if (p->spp == 0) return fail(RT_ERR_INVALID, "rt_render_queue: spp must be > 0");
+    QueueMode qm{(uint32_t *)cursors, rank, nranks};
+    return render_tiles_impl(c, tiles, ntiles, tile_w, tile_h, p, &qm);
+}
+
+int rt_resolve_tiles_to(rt_ctx *c, void *rgb8_frame)
+{
+    if (!c || !c->d_accum) return fail(RT_ERR_INVALID, "rt_resolve_tiles_to: no framebuffer");
+    if (!c->feed_valid) return fail(RT_ERR_INVALID, "rt_resolve_tiles_to: no rt_render_queue launch to resolve");
+    CK(enter_ctx(c));
+    CK(rt_launch_resolve_tiles(c->d_accum, c->W, c->feed_tiles, c->d_feed->slot, c->feed_slots, c->feed_TP,
+                               rgb8_frame ? (unsigned char *)rgb8_frame : c->d_rgb8, c->stream));
+    c->hs.launches += 1;
+    return RT_OK;
+}
+
+int rt_queue_tiles_rendered(rt_ctx *c, uint32_t *count)
+{
+    if (!c || !count || !c->feed_valid) return fail(RT_ERR_INVALID, "rt_queue_tiles_rendered: no rt_render_queue launch");
+    CK(enter_ctx(c));
+    CK(cudaStreamSynchronize(c->stream));
+    std::vector<uint32_t> h(c->feed_slots);
+    CK(cudaMemcpy(h.data(), c->d_feed->slot, (size_t)c->feed_slots * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    uint32_t n = 0;
+    for (uint32_t v : h) if (v < RT_FEED_NONE) ++n;
+    *count = n;
+    return drain_events(c);
+}
+
+int rt_copy_rgb8(rt_ctx *c, uint8_t *dst)
+{
+    if (!c || !dst || !c->d_rgb8) return fail(RT_ERR_INVALID, "rt_copy_rgb8: NULL argument or no framebuffer");
+    CK(enter_ctx(c));
+    size_t bytes = (size_t)c->W * c->H * 3;
+    int r = ensure_pinned(c, bytes);
+    if (r) return r;
+    CK(cudaMemcpyAsync(c->h_pin, c->d_rgb8, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    std::memcpy(dst, c->h_pin, bytes);
+    return drain_events(c);
+}
+
+int rt_ipc_export(rt_ctx *c, void *devptr, unsigned char handle[RT_IPC_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    if (!c || !devptr || !handle) return fail(RT_ERR_INVALID, "rt_ipc_export: NULL argument");
+    CK(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, devptr));
+    std::memcpy(handle, &h, sizeof h);
+    return RT_OK;
+}
+
+int rt_ipc_import(rt_ctx *c, const unsigned char handle[RT_IPC_HANDLE_BYTES], void **devptr)
+{
+    if (!c || !devptr || !handle) return fail(RT_ERR_INVALID, "rt_ipc_import: NULL argument");
+    CK(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    CK(cudaIpcOpenMemHandle(devptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+
+int rt_ipc_close(rt_ctx *c, void *devptr)
+{
+    if (!c || !devptr) return fail(RT_ERR_INVALID, "rt_ipc_close: NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaIpcCloseMemHandle(devptr));
+    return RT_OK;
 }
 
 int rt_stats_get(rt_ctx *c, rt_stats *out)

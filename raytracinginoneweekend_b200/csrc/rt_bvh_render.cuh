@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
     S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
     S.ar = S.ag = S.ab = 1.f;
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     BvhTrav T;
     T.node = 0; T.sp = 0; T.best_t = FLT_MAX; T.best_i = -1; T.a = 0.f; T.ix = T.iy = T.iz = 0.f; T.active = false;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
         if (!hold) {
             T.best_t = FLT_MAX; T.best_i = -1;
             if (S.st == ST_ACTIVE) {
-                T.a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+                T.a = ray_a(S.dx, S.dy, S.dz);
                 if (T.a > 0.f && T.a < 3.0e38f) {       // d = 0 or non-finite: the reference test finds nothing
                     T.ix = 1.f / S.dx; T.iy = 1.f / S.dy; T.iz = 1.f / S.dz;
                     T.node = sc.bvh_root; T.sp = 0; T.active = true;

@@ -14,6 +14,9 @@ size_t rt_render_smem_bytes(uint32_t npad, uint32_t nfilt, bool exact, bool lbvh
 size_t rt_render_tc_smem_bytes(uint32_t npad, uint32_t tc_ns, uint32_t m, bool *mats_in_smem)
 {
     size_t b = 512 + (size_t)tc_ns * 8u * 16u + (size_t)npad * 16u + (size_t)(tc_ns / 32u) * (RT_TC_WGS * 128u) * 4u;
+#if RT_TC_REGROUP
+    b += (size_t)RT_TC_WGS * 20u * 4u + (size_t)15 * (RT_TC_WGS * 128u) * 4u;   // regrouping prototype: key counts + exchange buffers
+#endif
     const size_t extra = (size_t)m * 16u + (size_t)npad * 8u;
     const bool fits = b + extra <= RT_TC_SMEM_LIMIT;
     if (mats_in_smem) *mats_in_smem = fits;
@@ -89,6 +92,80 @@ __global__ void k_resolve(const unsigned long long *__restrict__ accum, unsigned
             if (meanf) meanf[3ull * i0 + k] = mean[k];
         }
     }
+}
+
+// ---------------------------------------------------------------- device-side tile queue (multi-GPU), see rt_types.h
+// cursor of range r = first tile of the range, r * ntiles / nranks
+__global__ void k_queue_reset(uint32_t *cursors, uint32_t ntiles, uint32_t nranks)
+{
+    const uint32_t r = threadIdx.x;
+    if (r < nranks) cursors[r * RT_QUEUE_STRIDE] = (uint32_t)(((unsigned long long)r * ntiles) / nranks);
+}
+// count += spp on every pixel of the tiles this GPU acquired (the feed's slot table, read after the render kernel)
+__global__ void k_add_count_feed(unsigned long long *accum, uint32_t W, const uint4 *tiles, const uint32_t *slots,
+                                 uint32_t TP, unsigned long long spp)
+{
+    const uint32_t t = slots[blockIdx.y];
+    if (t >= RT_FEED_NONE) return;
+    const uint4 T = tiles[t];
+    const uint32_t npx = T.z * T.w;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < npx; r += gridDim.x * blockDim.x) {
+        const uint32_t ty = r / T.z, tx = r - ty * T.z;
+        accum[4ull * ((unsigned long long)(T.y + ty) * W + T.x + tx) + 3] += spp;
+    }
+}
+// Resolve (mean -> gamma -> 8 bit) the tiles this GPU rendered and store the texels into `dst`: this GPU's own RGB8 buffer,
+// or RANK 0's frame mapped over NVLink (peer access / CUDA IPC) -- the gather of the multi-GPU frame is this store.
+// One thread per 4 consecutive pixels of a tile row when the tile is 4-aligned (12-byte stores, 384 contiguous bytes per
+// warp), single pixels otherwise.
+__global__ void k_resolve_tiles(const unsigned long long *__restrict__ accum, uint32_t W, const uint4 *__restrict__ tiles,
+                                const uint32_t *__restrict__ slots, unsigned char *__restrict__ dst)
+{
+    const uint32_t t = slots[blockIdx.y];
+    if (t >= RT_FEED_NONE) return;
+    const uint4 T = tiles[t];
+    float mean[3];
+    if (((T.x | T.z | W) & 3u) == 0u) {
+        const uint32_t qw = T.z >> 2, nq = qw * T.w;
+        for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += gridDim.x * blockDim.x) {
+            const uint32_t ty = q / qw, tx = (q - ty * qw) << 2;
+            const unsigned long long p = (unsigned long long)(T.y + ty) * W + T.x + tx;
+            __align__(16) unsigned char u8[12];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) resolve_pixel(accum + 4ull * (p + k), mean, u8 + 3 * k);
+            uint32_t *d = reinterpret_cast<uint32_t *>(dst + 3ull * p);
+            const uint32_t *s = reinterpret_cast<const uint32_t *>(u8);
+            d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
+        }
+    } else {
+        const uint32_t npx = T.z * T.w;
+        for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < npx; r += gridDim.x * blockDim.x) {
+            const uint32_t ty = r / T.z, tx = r - ty * T.z;
+            const unsigned long long p = (unsigned long long)(T.y + ty) * W + T.x + tx;
+            unsigned char u8[3];
+            resolve_pixel(accum + 4ull * p, mean, u8);
+            dst[3ull * p] = u8[0]; dst[3ull * p + 1] = u8[1]; dst[3ull * p + 2] = u8[2];
+        }
+    }
+}
+cudaError_t rt_launch_queue_reset(uint32_t *cursors, uint32_t ntiles, uint32_t nranks, cudaStream_t s)
+{
+    k_queue_reset<<<1, 64, 0, s>>>(cursors, ntiles, nranks);
+    return cudaGetLastError();
+}
+cudaError_t rt_launch_add_count_feed(unsigned long long *accum, uint32_t W, const uint4 *tiles, const uint32_t *slots,
+                                     uint32_t nslots, uint32_t TP, unsigned long long spp, cudaStream_t s)
+{
+    if (!nslots) return cudaSuccess;
+    k_add_count_feed<<<dim3((TP + 1023) / 1024, nslots), 256, 0, s>>>(accum, W, tiles, slots, TP, spp);
+    return cudaGetLastError();
+}
+cudaError_t rt_launch_resolve_tiles(const unsigned long long *accum, uint32_t W, const uint4 *tiles, const uint32_t *slots,
+                                    uint32_t nslots, uint32_t TP, unsigned char *dst, cudaStream_t s)
+{
+    if (!nslots) return cudaSuccess;
+    k_resolve_tiles<<<dim3((TP / 4 + 255) / 256, nslots), 256, 0, s>>>(accum, W, tiles, slots, dst);
+    return cudaGetLastError();
 }
 
 // FP32 peak probe: 8 independent FMA chains per thread, 4096 x 8 FMAs each, full occupancy.

@@ -1,16 +1,16 @@
-// rt_device.cuh -- device code of the path-tracing hot path, compiled TWICE, both times with nvcc --fmad=false
-// (the compiler never fuses a multiply and an add on its own; every fused multiply-add below is an explicit fmaf):
-//   rt_kernels_exact.cu : -DRT_EXACT=1 -> namespace rtx.  The straightforward parity kernels: every float operation is an
-//                         IEEE mul/add/div/sqrt in the reference's operation order; results are bit-identical to the CPU
-//                         oracle (oracle/rt_oracle.c) path by path.
-//   rt_kernels_fast.cu  : -DRT_EXACT=0 -> namespace rtf.  The throughput kernels.  The CLOSEST HIT is the same IEEE
-//                         arithmetic (a conservative filter -- tensor cores or explicit FMA chains -- only selects the
-//                         candidates; the reference test decides), so hit index, t and normal are bit-identical to the
-//                         oracle for the same ray.  Shading comes in two instantiations (template parameter PAR):
-//                         PAR = true is the parity arithmetic of rtx (rejection sampler, IEEE normalise / divide, Schlick in
-//                         double) and renders bit-identically to the oracle; PAR = false samples the unit ball by inversion
-//                         and uses rsqrt / reciprocal in the normalisations (the timed default; same law, checked
-//                         statistically).
+// rt_device.cuh -- device code of the path-tracing hot path, compiled TWICE:
+//   rt_kernels_exact.cu : -DRT_EXACT=1, nvcc --fmad=false -> namespace rtx.  The parity kernels: every float operation is an
+//                         IEEE mul/add/div/sqrt in the reference's operation order (rejection sampler, IEEE normalise /
+//                         divide, Schlick in double); renders are bit-identical to the CPU oracle (oracle/rt_oracle.c) path
+//                         by path.  Includes the tensor-core kernel (rt_tensor.cuh) with this shading: RT_FLAG_EXACT on a
+//                         48..1024-sphere scene runs the timed kernel's structure and closest hit.
+//   rt_kernels_fast.cu  : -DRT_EXACT=0, FMA contraction on -> namespace rtf.  The throughput kernels.  The CLOSEST HIT is
+//                         written with explicit round-to-nearest intrinsics (__fmul_rn, __fadd_rn, __fsqrt_rn, __fdiv_rn:
+//                         never contracted), so it is the same IEEE arithmetic in both units: a conservative filter --
+//                         tensor cores or explicit FMA chains -- only selects the candidates, the reference test decides,
+//                         and hit index, t and normal are bit-identical to the oracle for the same ray.  The shading of this
+//                         unit samples the unit ball by inversion, uses rsqrt / reciprocal in the normalisations and lets
+//                         the compiler contract (the timed default; same law, checked statistically).
 //
 // Reference semantics restated here (paths relative to the reference repo):
 //   intersect            src/raytracer.hxx:52-92      hit_world (first minimum)   src/raytracer.hxx:94-118
@@ -208,31 +208,92 @@ __device__ __forceinline__ float schlick(float ri, float cosine)
 }
 
 // ------------------------------------------------------------------ closest hit, brute force
-// One sphere test: the arithmetic of src/raytracer.hxx:55-61, every operation a separate IEEE multiply / add in the
-// reference's order (both translation units are compiled with --fmad=false), s.w = radius * radius.
+// The reference test, src/raytracer.hxx:55-89, in explicit round-to-nearest intrinsics: every operation is a separate IEEE
+// multiply / add / sqrt / divide in the reference's order, whatever the translation unit's contraction setting.
+// a = dot(d, d), src/raytracer.hxx:56
+__device__ __forceinline__ float ray_a(float dx, float dy, float dz)
+{
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+// oc, b, c and the discriminant b*b - a*c (src/raytracer.hxx:55-61); s.w = radius * radius
+__device__ __forceinline__ float sphere_disc(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
+                                             float a, float &b, float &c)
+{
+    const float ocx = __fsub_rn(ox, s.x), ocy = __fsub_rn(oy, s.y), ocz = __fsub_rn(oz, s.z);
+    b = __fadd_rn(__fadd_rn(__fmul_rn(ocx, dx), __fmul_rn(ocy, dy)), __fmul_rn(ocz, dz));
+    c = __fsub_rn(__fadd_rn(__fadd_rn(__fmul_rn(ocx, ocx), __fmul_rn(ocy, ocy)), __fmul_rn(ocz, ocz)), s.w);
+    return __fsub_rn(__fmul_rn(b, b), __fmul_rn(a, c));
+}
 __device__ __forceinline__ float sphere_disc(float4 s, float ox, float oy, float oz, float dx, float dy, float dz,
                                              float a, float &b)
 {
-    float ocx = ox - s.x, ocy = oy - s.y, ocz = oz - s.z;
-    b = ocx * dx + ocy * dy + ocz * dz;
-    float c = (ocx * ocx + ocy * ocy + ocz * ocz) - s.w;
-    return b * b - a * c;
+    float c;
+    return sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
 }
 
-// Exact per-candidate test (src/raytracer.hxx:63-89) against the running closest hit.  Candidates are
+// Early-outs of the throughput kernels' candidate test.  Each one only SKIPS work whose outcome is already decided: when
+// it fires, the plain reference test below would leave (best_t, best_i) untouched, so the result stays the oracle's bit for
+// bit (RT_FLAG_FILTER_CHECK compares against the plain test over all spheres for every segment).
+//   bit 0  b > 0 and c > 0: the origin is outside the sphere and the sphere lies behind the ray.  a c >= 0 makes
+//          disc = RN(RN(b b) - RN(a c)) <= RN(b b), so sq = RN(sqrt(disc)) <= RN(sqrt(RN(b b))) = b and both roots
+//          (-b -+ sq) / a are <= 0 < kMIN in the reference's own float arithmetic.  (The tensor / FMA filters test the
+//          LINE, so spheres behind a bounce ray's origin are candidates: this saves their sqrt and two divisions.)
+//   bit 1  approximate roots with an error bound.  t1', t2' from sqrt.approx / rcp.approx differ from the IEEE roots by
+//          less than m = 2^-19 (|b| + sq) / a (derivation: DESIGN.md section 4; the individual errors add up to < 2^-20).
+//          Skip when the smallest root that can still be valid is beyond the running best (t' - m > best_t: a loser) or
+//          when even t2' + m < kMIN (both roots invalid: the sphere the path just left).  NaN / inf in the approximation
+//          make every comparison false, i.e. fall through to the IEEE evaluation.
+#ifndef RT_CAND_EARLYOUT
+#define RT_CAND_EARLYOUT 3
+#endif
+__device__ __forceinline__ bool candidate_decided(float disc, float b, float c, float a, float best_t)
+{
+#if !RT_EXACT
+    if ((RT_CAND_EARLYOUT & 1) && b > 0.f && c > 0.f) return true;
+    if (RT_CAND_EARLYOUT & 2) {
+        float sq, ra;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(disc));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(a));
+        const float m = (fabsf(b) + sq) * ra * 1.9073486328125e-6f;                 // 2^-19
+        const float t1 = (-b - sq) * ra, t2 = (sq - b) * ra;
+        if (t2 + m < RT_KMIN) return true;                                          // both roots below kMIN
+        const float tl = (t1 + m < RT_KMIN) ? t2 : t1;                             // smallest root that can still be valid
+        if (tl - m > best_t) return true;                                           // cannot beat the running closest hit
+    }
+#endif
+    return false;
+}
+
+// Per-candidate reference test (src/raytracer.hxx:63-89) against the running closest hit.  Candidates are
 // visited in increasing sphere index and the comparison is strict, so ties keep the LOWEST index --
 // hit_world's stable_partition + first min_element (src/raytracer.hxx:107-117).
-__device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz,
-                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i)
+// sphere_candidate_ref is the plain test; sphere_candidate adds the early-outs above in the throughput unit.
+__device__ __forceinline__ void sphere_candidate_ref(float4 s, int j, float ox, float oy, float oz,
+                                                     float dx, float dy, float dz, float a, float &best_t, int &best_i)
 {
     float b;
     float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
     if (disc > 0.f) {
-        float sq = sqrtf(disc);
-        float t = (-b - sq) / a;
+        float sq = __fsqrt_rn(disc);
+        float t = __fdiv_rn(__fsub_rn(-b, sq), a);
         if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
         else {
-            t = (-b + sq) / a;
+            t = __fdiv_rn(__fadd_rn(-b, sq), a);
+            if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        }
+    }
+}
+__device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz,
+                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i)
+{
+    float b, c;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
+    if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
+        float sq = __fsqrt_rn(disc);
+        float t = __fdiv_rn(__fsub_rn(-b, sq), a);
+        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        else {
+            t = __fdiv_rn(__fadd_rn(-b, sq), a);
             if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
         }
     }
@@ -256,7 +317,7 @@ __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_s
     uint32_t nz[R];                                  // bit (31 - w): mask word w of the chunk is non-empty
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        a[r] = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+        a[r] = ray_a(dx[r], dy[r], dz[r]);
         best_t[r] = FLT_MAX;
         best_i[r] = -1;
         nz[r] = 0u;
@@ -376,7 +437,7 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
     if (n <= RT_SMALL_SCENE) {                       // a handful of spheres: the candidate test on each one costs less than one filter group
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+            const float a = ray_a(dx[r], dy[r], dz[r]);
             if (live[r] && a > 0.f && a < 3.0e38f)
                 for (uint32_t j = 0; j < n; ++j)
                     sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, best_t[r], best_i[r]);
@@ -412,7 +473,7 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
         // one candidate per lane per iteration: the warp iterates max-over-lanes of the candidate COUNT
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+            const float a = ray_a(dx[r], dy[r], dz[r]);
             uint32_t words = nz[r], cand = 0, w = 0;
             nz[r] = 0u;
             for (;;) {
@@ -452,13 +513,13 @@ __device__ __forceinline__ void bvh_leaf_sphere(const RtDeviceScene &sc, uint32_
                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i, BvhCounters &cnt)
 {
     ++cnt.leaves;
-    float b;
-    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b);
-    if (disc > 0.f) {
-        float sq = sqrtf(disc);
-        float t = (-b - sq) / a;
+    float b, c;
+    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
+    if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
+        float sq = __fsqrt_rn(disc);
+        float t = __fdiv_rn(__fsub_rn(-b, sq), a);
         bool ok = t < FLT_MAX && t > RT_KMIN;
-        if (!ok) { t = (-b + sq) / a; ok = t < FLT_MAX && t > RT_KMIN; }
+        if (!ok) { t = __fdiv_rn(__fadd_rn(-b, sq), a); ok = t < FLT_MAX && t > RT_KMIN; }
         if (ok && t <= best_t) {
             const int j = (int)__ldg(sc.bvh_prims + pos);
             if (t < best_t || j < best_i) { best_t = t; best_i = j; }
@@ -535,7 +596,7 @@ __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool l
 {
     best_t = FLT_MAX;
     best_i = -1;
-    const float a = dx * dx + dy * dy + dz * dz;
+    const float a = ray_a(dx, dy, dz);
     if (!live || !(a > 0.f) || !(a < 3.0e38f)) return;      // d = 0 or non-finite: the reference test finds nothing
     const float ix = 1.f / dx, iy = 1.f / dy, iz = 1.f / dz;
     uint32_t stack[96];
@@ -568,9 +629,85 @@ __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool l
 // A warp takes RT_BATCH consecutive work items (pixel, sample) with one atomic and deals them to the
 // lanes whose path ended, by ballot + popc prefix -- terminated paths are replaced immediately, so every
 // lane carries a live ray into the next sphere loop (compaction by regeneration).
-struct WarpPool { uint32_t next, end; bool exhausted; };
+struct WarpPool { uint32_t next, end, tile; bool exhausted; };
 
-__device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, uint32_t *counter, uint32_t total)
+// ---- device-side tile queue (multi-GPU): acquire the next tile for this GPU -- own range first, then steal.
+// Range r = tiles [r T / N, (r+1) T / N) of the frame's (interleaved) tile list; cursors live in rank 0's memory.
+__device__ __forceinline__ uint32_t queue_fetch(const RtRenderArgs &A)
+{
+    if (*reinterpret_cast<volatile uint32_t *>(&A.feed->drained)) return RT_FEED_NONE;
+    for (uint32_t d = 0; d < A.q_nranks; ++d) {
+        const uint32_t v = (A.q_rank + d) % A.q_nranks;
+        const uint32_t hi = (uint32_t)(((unsigned long long)(v + 1u) * A.q_ntiles) / A.q_nranks);
+        uint32_t *cur = A.q_cursors + v * RT_QUEUE_STRIDE;
+        if (d > 0u && *reinterpret_cast<volatile uint32_t *>(cur) >= hi) continue;     // a dry victim: do not bump it again
+        const uint32_t t = atomicAdd_system(cur, 1u);
+        if (t < hi) return t;
+    }
+    A.feed->drained = 1u;
+    return RT_FEED_NONE;
+}
+// tile of feed slot k (called by ONE lane): the first warp to reach a slot talks to the queue, the others wait for it
+__device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, unsigned long long k)
+{
+    if (k >= A.feed_slots) return RT_FEED_NONE;
+    uint32_t *slot = A.feed->slot + k;
+    uint32_t v = *reinterpret_cast<volatile uint32_t *>(slot);
+    if (v == RT_FEED_EMPTY) {
+        v = atomicCAS(slot, RT_FEED_EMPTY, RT_FEED_FETCHING);
+        if (v == RT_FEED_EMPTY) {
+            v = queue_fetch(A);
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t *>(slot) = v;
+            return v;
+        }
+    }
+    while (v == RT_FEED_FETCHING) {
+        __nanosleep(200);
+        v = *reinterpret_cast<volatile uint32_t *>(slot);
+    }
+    return v;
+}
+
+// Next batch of work items for the warp (rare: once per RT_BATCH items; kept out of line so that the queue code does not
+// cost the hot loops registers).  Returns false when there is no more work.
+#ifndef RT_POOL_REFILL_INLINE
+#define RT_POOL_REFILL_INLINE 0
+#endif
+#if RT_POOL_REFILL_INLINE
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+bool pool_refill(WarpPool &p, const RtRenderArgs &A)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    if (A.feed) {
+        // queue mode: a batch of the feed's virtual item space lies inside ONE slot (TPS is a multiple of RT_BATCH)
+        uint32_t t = RT_FEED_NONE, j = 0;
+        if (lane == 0) {
+            const unsigned long long base = atomicAdd(&A.feed->next_item, (unsigned long long)RT_BATCH);
+            const unsigned long long k = base / A.TPS;
+            j = (uint32_t)(base - k * A.TPS);
+            t = feed_slot_tile(A, k);
+        }
+        t = __shfl_sync(RT_FULL, t, 0);
+        j = __shfl_sync(RT_FULL, j, 0);
+        if (t >= RT_FEED_NONE) return false;
+        p.next = j; p.end = j + RT_BATCH; p.tile = t;
+        return true;
+    }
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(A.work_counter, RT_BATCH);
+    base = __shfl_sync(RT_FULL, base, 0);
+    if (base >= A.total_items) return false;
+    p.next = base;
+    p.end = min(base + RT_BATCH, A.total_items);
+    return true;
+}
+
+// Work items for the lanes that want one; `tile` = the item's tile in queue mode (items are then tile-relative).
+__device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, const RtRenderArgs &A, uint32_t &tile)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt = (1u << lane) - 1u;
@@ -579,17 +716,12 @@ __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, uint32_t *
     while (need) {
         if (p.next >= p.end) {
             if (p.exhausted) break;
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(counter, RT_BATCH);
-            base = __shfl_sync(RT_FULL, base, 0);
-            if (base >= total) { p.exhausted = true; break; }
-            p.next = base;
-            p.end = min(base + RT_BATCH, total);
+            if (!pool_refill(p, A)) { p.exhausted = true; break; }
         }
         uint32_t avail = p.end - p.next;
         bool mine = want && item == 0xffffffffu;
         uint32_t rank = __popc(need & lt);
-        if (mine && rank < avail) item = p.next + rank;
+        if (mine && rank < avail) { item = p.next + rank; tile = p.tile; }
         p.next += min((uint32_t)__popc(need), avail);
         need = __ballot_sync(RT_FULL, want && item == 0xffffffffu);
     }
@@ -697,13 +829,14 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     uint32_t px = 0, py = 0;
     uint32_t ev = S.bounce + 1u;
     for (bool need = want;;) {
-        uint32_t item = pool_take(pool, need, A.work_counter, A.total_items);
+        uint32_t qtile = 0u;
+        uint32_t item = pool_take(pool, need, A, qtile);
         if (need) {
             if (item != 0xffffffffu) {
                 // item order: tile-major, then sample, then pixel -- a tile's accumulators (TP * 32 B) stay
-                // cache-resident while all of its samples are traced
+                // cache-resident while all of its samples are traced.  Queue mode: the item is already tile-relative.
                 uint32_t q, r, rx;
-                uint32_t tl = (A.TPS > 1u) ? div_magic(item, A.TPS, A.mTPS, q) : (q = 0u, item);
+                uint32_t tl = A.feed ? (q = item, qtile) : (A.TPS > 1u) ? div_magic(item, A.TPS, A.mTPS, q) : (q = 0u, item);
                 uint32_t s_i = (A.TP > 1u) ? div_magic(q, A.TP, A.mTP, r) : (r = 0u, q);
                 uint4 T = A.tiles ? __ldg(A.tiles + A.t0 + tl) : A.tile0;
                 if (r < T.z * T.w) {                                      // edge tiles leave slots unused
@@ -855,7 +988,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         S[r].ox = S[r].oy = S[r].oz = 0.f; S[r].dx = S[r].dy = S[r].dz = 0.f;
         S[r].ar = S[r].ag = S[r].ab = 1.f;
     }
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     float best_t[RT_RPT]; int best_i[RT_RPT];
 #pragma unroll
@@ -892,10 +1025,10 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
 #pragma unroll
                 for (int r = 0; r < RT_RPT; ++r) {
                     if (!live[r]) continue;
-                    const float a = dx[r] * dx[r] + dy[r] * dy[r] + dz[r] * dz[r];
+                    const float a = ray_a(dx[r], dy[r], dz[r]);
                     float ct = FLT_MAX; int ci = -1;
                     for (uint32_t j = 0; j < A.sc.n; ++j)
-                        sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, ct, ci);
+                        sphere_candidate_ref(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, ct, ci);
                     if (ci != best_i[r] || ct != best_t[r]) atomicAdd(A.stats + 7, 1ull);
                 }
             }
@@ -946,14 +1079,14 @@ __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(cons
     S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
     S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
     S.ar = S.ag = S.ab = 1.f;
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     float best_t = FLT_MAX; int best_i = -1;
     for (;;) {
         shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts, false, s_rad, s_meta, mats ? s_mat : nullptr);
         if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
         best_t = FLT_MAX; best_i = -1;
-        const float a = S.dx * S.dx + S.dy * S.dy + S.dz * S.dz;
+        const float a = ray_a(S.dx, S.dy, S.dz);
         if (S.st == ST_ACTIVE && a > 0.f && a < 3.0e38f) {
             for (uint32_t j = 0; j < n; ++j)
                 sphere_candidate(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, best_t, best_i);
@@ -984,14 +1117,14 @@ __device__ __forceinline__ void hits_ray(const RtHitArgs &A, unsigned long long 
         ox = r[0]; oy = r[1]; oz = r[2]; dx = r[3]; dy = r[4]; dz = r[5];
     } else {
         uint32_t ty = (uint32_t)(i / A.w), tx = (uint32_t)(i - (unsigned long long)ty * A.w);
-        float u = (float)(A.x0 + tx) / (float)A.W;
-        float v = (float)(A.y0 + ty) / (float)A.H;
-        float omv = 1.f - v;
+        float u = __fdiv_rn((float)(A.x0 + tx), (float)A.W);
+        float v = __fdiv_rn((float)(A.y0 + ty), (float)A.H);
+        float omv = __fsub_rn(1.f, v);
         const RtDeviceCamera &c = A.cam;
         ox = c.ox; oy = c.oy; oz = c.oz;
-        dx = (c.llx + c.hx * u) + c.vx * omv;
-        dy = (c.lly + c.hy * u) + c.vy * omv;
-        dz = (c.llz + c.hz * u) + c.vz * omv;
+        dx = __fadd_rn(__fadd_rn(c.llx, __fmul_rn(c.hx, u)), __fmul_rn(c.vx, omv));
+        dy = __fadd_rn(__fadd_rn(c.lly, __fmul_rn(c.hy, u)), __fmul_rn(c.vy, omv));
+        dz = __fadd_rn(__fadd_rn(c.llz, __fmul_rn(c.hz, u)), __fmul_rn(c.vz, omv));
     }
 }
 // hit record of src/raytracer.hxx:66-72: index, t, normal = (o + d t - c) / r (s = the sphere record when bi >= 0)
@@ -1001,20 +1134,18 @@ __device__ __forceinline__ void hits_store(const RtHitArgs &A, unsigned long lon
     A.idx[i] = bi;
     if (bi >= 0) {
         float rad = __ldg(A.sc.sph_rad + bi);
-        float px = ox + dx * bt, py = oy + dy * bt, pz = oz + dz * bt;
+        float px = __fadd_rn(ox, __fmul_rn(dx, bt)), py = __fadd_rn(oy, __fmul_rn(dy, bt)), pz = __fadd_rn(oz, __fmul_rn(dz, bt));
         A.t[i] = bt;
-        A.normal[3 * i + 0] = (px - s.x) / rad;
-        A.normal[3 * i + 1] = (py - s.y) / rad;
-        A.normal[3 * i + 2] = (pz - s.z) / rad;
+        A.normal[3 * i + 0] = __fdiv_rn(__fsub_rn(px, s.x), rad);
+        A.normal[3 * i + 1] = __fdiv_rn(__fsub_rn(py, s.y), rad);
+        A.normal[3 * i + 2] = __fdiv_rn(__fsub_rn(pz, s.z), rad);
     } else {
         A.t[i] = 0.f;
         A.normal[3 * i + 0] = 0.f; A.normal[3 * i + 1] = 0.f; A.normal[3 * i + 2] = 0.f;
     }
 }
 
-#if !RT_EXACT
 #include "rt_tensor.cuh"
-#endif
 #include "rt_bvh_render.cuh"
 
 // ------------------------------------------------------------------ parity pass: primary / caller-supplied rays

@@ -1,5 +1,5 @@
-// Parity build of the hot path: compiled with --fmad=false (see Makefile) so every float operation
-// is a separate IEEE-754 multiply/add in the reference's order.  Namespace rtx.
+// Parity kernels of the hot path (namespace rtx): compiled with --fmad=false (see Makefile) so every float operation is a
+// separate IEEE-754 multiply/add in the reference's order; includes the tensor-core kernel with the parity shading.
 #define RT_EXACT 1
 #include "rt_device.cuh"
 #include "rt_launch.inc"

@@ -1,5 +1,6 @@
 // rt_tensor.cuh -- brute-force closest hit with the candidate filter on the 5th-generation tensor cores.
-// Included by rt_device.cuh in the throughput translation unit only (namespace rtf).
+// Included by rt_device.cuh in BOTH translation units: rtf::k_render_tc is the timed kernel (throughput shading),
+// rtx::k_render_tc the same kernel with the parity shading (RT_FLAG_EXACT; renders bit-identical to the oracle).
 //
 // What is computed.  For a ray (o, u = d/|d|) and a sphere (c, r) the sign of the discriminant of
 // src/raytracer.hxx:55-61 is the sign of
@@ -323,7 +324,7 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
     }
     uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
     best_t = FLT_MAX; best_i = -1;
-    const float a = dx * dx + dy * dy + dz * dz;            // src/raytracer.hxx:56, the reference's operation order
+    const float a = ray_a(dx, dy, dz);                      // src/raytracer.hxx:56, the reference's operation order
     for (uint32_t t = 0; t < c.nch; ++t) {
         const uint32_t b = t % RT_TC_NBUF;
         bar_wait(r.bar + 1 + b, (r.full_parity >> b) & 1u);
@@ -347,6 +348,15 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
             if (m0) { c.s_mask[w0 * RT_TC_RAY_THREADS + r.tid] = m0; nz |= 0x80000000u >> w0; }
             const uint32_t m1 = sign_mask(v1);
             if (m1) { c.s_mask[(w0 + 1u) * RT_TC_RAY_THREADS + r.tid] = m1; nz |= 0x80000000u >> (w0 + 1u); }
+#if RT_TC_SKIPSTAT
+            // measurement build (two-level filter question): how often does a WHOLE WARP find no candidate in a 64-sphere tile,
+            // i.e. how often could a warp-collective tcgen05.ld + sign-mask pass be skipped?  counts land in the otherwise unused
+            // node_visits (warp-tiles seen) and filter_misses (warp-tiles with no candidate in any lane) statistics
+            {
+                const bool none = !__any_sync(RT_FULL, live && (m0 | m1) != 0u);
+                if (r.lane == 0) { atomicAdd(stats + 5, 1ull); if (none) atomicAdd(stats + 7, 1ull); }
+            }
+#endif
         }
     }
     // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
@@ -367,16 +377,73 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
     if (check && live) {                    // self-check: the same test over all spheres must agree
         float ct = FLT_MAX; int ci = -1;
         for (uint32_t j = 0; j < c.n; ++j)
-            sphere_candidate(c.s_sph[j], (int)j, ox, oy, oz, dx, dy, dz, a, ct, ci);
+            sphere_candidate_ref(c.s_sph[j], (int)j, ox, oy, oz, dx, dy, dz, a, ct, ci);
         if (ci != best_i || ct != best_t) atomicAdd(stats + 7, 1ull);
     }
 }
 
+#if RT_TC_REGROUP
+// ---------------------------------------------------------------- material regrouping (north_star (3); prototype, default off)
+// After the closest hit the 128 paths of a warpgroup are SORTED by what their shading will do -- lambert / metal /
+// dielectric hit, sky or depth cap, regeneration -- so that each warp shades (mostly) one kind.  With one path per lane a
+// permutation inside a warp cannot reduce divergence, so the exchange goes through shared memory across the four warps:
+// per-warp ballots give the key counts, one named barrier publishes them, every thread computes its destination from
+// the 4 x 5 counts, writes its 15 words of state (13 of the path, t, hit index) there, a second barrier, reads its new
+// state back.  Measured against the unsorted kernel in DESIGN.md section 4 (tools/build_variant.sh regroup -DRT_TC_REGROUP=1).
+#define RT_TC_XCHG_WORDS 15
+__device__ __forceinline__ void regroup(const RtRenderArgs &A, const RayWarp &r, uint32_t *s_cnt, uint32_t *s_x,
+                                        const uint32_t *s_meta, PathSlot &S, float &best_t, int &best_i)
+{
+    const uint32_t w = (r.tid >> 5) & 3u, lane = r.lane, lt = (1u << lane) - 1u;
+    uint32_t key;
+    if (S.st != ST_ACTIVE) key = 4u;                                         // will regenerate
+    else if (best_i < 0 || S.bounce + 1u >= A.depth) key = 3u;               // sky / depth cap: the short branches
+    else key = (s_meta ? s_meta[best_i] : __ldg(A.sc.sph_meta + best_i)) >> 30;   // material kind of the hit
+    uint32_t mine = 0u, cnt[5];
+#pragma unroll
+    for (uint32_t k = 0; k < 5u; ++k) {
+        const uint32_t b = __ballot_sync(RT_FULL, key == k);
+        cnt[k] = __popc(b);
+        if (key == k) mine = __popc(b & lt);
+    }
+    uint32_t *wc = s_cnt + r.wg * 20u;                                       // [warp][key]
+    if (lane < 5u) wc[w * 5u + lane] = cnt[lane];
+    asm volatile("bar.sync %0, 128;" ::"r"(8u + r.wg) : "memory");
+    uint32_t pos = mine;
+#pragma unroll
+    for (uint32_t k = 0; k < 5u; ++k) {
+#pragma unroll
+        for (uint32_t ww = 0; ww < 4u; ++ww) {
+            const uint32_t v = wc[ww * 5u + k];
+            if (k < key || (k == key && ww < w)) pos += v;
+        }
+    }
+    uint32_t *x = s_x + r.wg * 128u;                                         // [word][RT_TC_RAY_THREADS]
+#define RT_X(i) x[(i) * RT_TC_RAY_THREADS + pos]
+    RT_X(0) = __float_as_uint(S.ox); RT_X(1) = __float_as_uint(S.oy); RT_X(2) = __float_as_uint(S.oz);
+    RT_X(3) = __float_as_uint(S.dx); RT_X(4) = __float_as_uint(S.dy); RT_X(5) = __float_as_uint(S.dz);
+    RT_X(6) = __float_as_uint(S.ar); RT_X(7) = __float_as_uint(S.ag); RT_X(8) = __float_as_uint(S.ab);
+    RT_X(9) = S.pix; RT_X(10) = S.smp; RT_X(11) = S.bounce | ((uint32_t)S.st << 30);
+    RT_X(12) = __float_as_uint(best_t); RT_X(13) = (uint32_t)best_i;
+#undef RT_X
+    asm volatile("bar.sync %0, 128;" ::"r"(8u + r.wg) : "memory");
+    const uint32_t me = r.tid & 127u;
+#define RT_Y(i) x[(i) * RT_TC_RAY_THREADS + me]
+    S.ox = __uint_as_float(RT_Y(0)); S.oy = __uint_as_float(RT_Y(1)); S.oz = __uint_as_float(RT_Y(2));
+    S.dx = __uint_as_float(RT_Y(3)); S.dy = __uint_as_float(RT_Y(4)); S.dz = __uint_as_float(RT_Y(5));
+    S.ar = __uint_as_float(RT_Y(6)); S.ag = __uint_as_float(RT_Y(7)); S.ab = __uint_as_float(RT_Y(8));
+    S.pix = RT_Y(9); S.smp = RT_Y(10);
+    const uint32_t bs = RT_Y(11);
+    S.bounce = bs & 0x3fffffffu; S.st = (int)(bs >> 30);
+    best_t = __uint_as_float(RT_Y(12)); best_i = (int)RT_Y(13);
+#undef RT_Y
+}
+#endif
+
 }  // namespace tc
 
 // ---------------------------------------------------------------- the persistent bounce loop on the tensor path
-// PAR = true: parity shading (bit-identical to the oracle; RT_FLAG_EXACT); PAR = false: throughput shading (the default).
-template <bool PAR>
+// Shading = that of the translation unit: rtf -- throughput shading (the timed default); rtx -- parity shading (RT_FLAG_EXACT).
 __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -408,11 +475,20 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
         S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
         S.ar = S.ag = S.ab = 1.f;
-        WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
+        WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
         ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
         float best_t = FLT_MAX; int best_i = -1;
+#if RT_TC_REGROUP
+        // exchange buffers of the regrouping prototype, behind everything else in the dynamic shared memory
+        uint32_t *s_cnt = reinterpret_cast<uint32_t *>(mats_in_smem ? reinterpret_cast<unsigned char *>(s_meta + c.npad)
+                                                                     : reinterpret_cast<unsigned char *>(s_mat));
+        uint32_t *s_x = s_cnt + RT_TC_WGS * 20u;
+#endif
         for (;;) {
-            shade_slot<false, PAR>(A, c.s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
+#if RT_TC_REGROUP
+            tc::regroup(A, rw, s_cnt, s_x, mats_in_smem ? s_meta : nullptr, S, best_t, best_i);
+#endif
+            shade_slot<false>(A, c.s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
                                    mats_in_smem ? s_meta : nullptr, mats_in_smem ? s_mat : nullptr);
             if (!tc::wg_any(1u + rw.wg, S.st != ST_EMPTY)) {                         // whole warpgroup out of work
                 tc::ray_warp_finish(c, rw);
@@ -437,6 +513,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 }
 
 // ---------------------------------------------------------------- parity pass through the SAME closest hit
+#if !RT_EXACT
 // rt_primary_hits / rt_closest_hits of the throughput build on a tensor-eligible scene: one ray per ray thread and pass,
 // grid-stride over the rays; tc::closest_hit is the function k_render_tc calls.
 __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_hits_tc(const __grid_constant__ RtHitArgs A)
@@ -471,3 +548,4 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_hits_tc(const __grid_const
     }
     tc::cta_teardown(c);
 }
+#endif  // !RT_EXACT

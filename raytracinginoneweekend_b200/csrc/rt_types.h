@@ -57,6 +57,23 @@ struct RtDeviceCamera {          // src/camera.hxx:66-76 derived state
     float bvx, bvy, bvz;
 };
 
+// Device-side tile queue (multi-GPU).  The frame's tile list is split into one contiguous range per rank;
+// the cursor of range r lives in RANK 0's memory (peer-mapped over NVLink: cudaDeviceEnablePeerAccess or CUDA IPC), one
+// 64-byte line each.  A persistent render kernel acquires tiles itself: own range first (atomicAdd at system scope on
+// its cursor), then it steals by advancing another range's cursor.  Locally the kernel keeps a FEED: a 64-bit item
+// counter over the virtual concatenation of the tiles this GPU acquired (slot k = the k-th acquired tile, TPS items
+// each) and the table slot -> tile, filled on demand by the first warp that reaches a slot.
+#define RT_FEED_EMPTY 0xffffffffu      // slot not acquired yet
+#define RT_FEED_FETCHING 0xfffffffeu   // a warp is talking to the queue for this slot
+#define RT_FEED_NONE 0xfffffffdu       // the queue was dry: no more tiles for this GPU
+#define RT_QUEUE_STRIDE 16u            // cursor r is at cursors[r * RT_QUEUE_STRIDE] (uint32, one 64-byte line each)
+struct RtTileFeed {
+    unsigned long long next_item;      // zeroed before the launch
+    uint32_t drained;                  // set once a fetch found every range dry
+    uint32_t pad;
+    uint32_t slot[1];                  // [nslots] RT_FEED_EMPTY before the launch; afterwards the tiles this GPU rendered
+};
+
 struct RtRenderArgs {
     RtDeviceScene sc;
     RtDeviceCamera cam;
@@ -79,6 +96,11 @@ struct RtRenderArgs {
     uint32_t check;              // RT_FLAG_FILTER_CHECK
     uint32_t book;               // RT_FLAG_BOOK_OPTICS
     uint32_t smem_mats;          // tensor kernel: radii, material indices and materials are staged in shared memory (they fit)
+    // device-side tile queue (feed == nullptr: the work domain is the tile list above)
+    RtTileFeed *feed;            // local feed of this launch
+    uint32_t feed_slots;
+    uint32_t *q_cursors;         // RT_QUEUE_STRIDE-strided range cursors in rank 0's memory (system-scope atomics)
+    uint32_t q_rank, q_nranks, q_ntiles;
 };
 
 struct RtHitArgs {
@@ -93,6 +115,7 @@ struct RtHitArgs {
 
 // launchers, one set per arithmetic mode (exact = --fmad=false TU, fast = FMA TU)
 namespace rtx {
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
 cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh);
 cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
@@ -104,7 +127,7 @@ cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
 namespace rtf {
-cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool parity);
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
 cudaError_t launch_hits_tc(const RtHitArgs &a, int grid, size_t smem, cudaStream_t s);
 cudaError_t launch_render_small(const RtRenderArgs &a, int grid, cudaStream_t s);
 cudaError_t small_occupancy(int *ctas_per_sm);
@@ -134,6 +157,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #endif
 #ifndef RT_TC_NBUF
 #define RT_TC_NBUF 1
+#endif
+#ifndef RT_TC_REGROUP
+#define RT_TC_REGROUP 0            // 1: material-regrouping prototype (north_star (3)): sort the 128 paths of a warpgroup by shading kind
 #endif
 #ifndef RT_TC_RAY_HINT
 #define RT_TC_RAY_HINT 0           // > 0: suspend-time hint (ns) of the ray warps' try_wait on an accumulator tile; 0 = bare spin

@@ -15,6 +15,10 @@ struct ctx_guard final {
     rt_ctx *ctx{nullptr};
     ~ctx_guard() { rt_destroy(ctx); }
 };
+struct multi_guard final {
+    rt_multi *m{nullptr};
+    ~multi_guard() { rt_multi_destroy(m); }
+};
 
 void check(int rc, char const *what)
 {
@@ -58,8 +62,6 @@ void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8ve
                              cam0.up().x, cam0.up().y, cam0.up().z,
                              cam0.aspect(), cam0.vFOV(), cam0.aperture(), cam0.focus_distance()};
 
-    ctx_guard g;
-    check(rt_create(&g.ctx, options.device), "rt_create");
     rt_render_params p{};
     p.spp = options.samples_per_pixel;
     p.max_depth = options.max_depth;
@@ -69,6 +71,18 @@ void cuda_impl(std::uint32_t width, std::uint32_t height, std::vector<math::u8ve
               (options.book_optics ? static_cast<std::uint32_t>(RT_FLAG_BOOK_OPTICS) : 0u);
     static_assert(sizeof(math::u8vec3) == 3, "texels are tightly packed RGB8");
     auto *texels = reinterpret_cast<std::uint8_t *>(image_texels.data());
+    if (options.devices.size() > 1 && options.samples_per_pass == 0) {
+        // N GPUs, one call: tiles of 128 x 64 pulled from the device-side queue, texels stored into the first device's frame
+        multi_guard mg;
+        check(rt_multi_create(&mg.m, options.devices.data(), static_cast<int>(options.devices.size())), "rt_multi_create");
+        check(rt_multi_render_frame(mg.m, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
+                                    static_cast<std::uint32_t>(materials.size()), cam13, width, height, &p, 128, 64,
+                                    options.gather_nccl ? static_cast<std::uint32_t>(RT_MULTI_GATHER_NCCL) : 0u, texels),
+              "rt_multi_render_frame");
+        return;
+    }
+    ctx_guard g;
+    check(rt_create(&g.ctx, options.devices.size() == 1 ? options.devices[0] : options.device), "rt_create");
     if (options.samples_per_pass == 0) {
         check(rt_render_frame(g.ctx, spheres.data(), static_cast<std::uint32_t>(spheres.size()), materials.data(),
                               static_cast<std::uint32_t>(materials.size()), cam13, width, height, &p, texels),

@@ -2,6 +2,7 @@
 // cuda_impl, write a P6 PPM), with the scene, size, spp and depth on the command line.
 //   rtiow_demo [--scene simple|huge|synthetic:N] [--width W] [--height H] [--spp S] [--depth D] [--seed X]
 //              [--exact] [--book-optics] [--out image.ppm] [--dump-scene file.bin]
+//              [--gpus N | --devices a,b,c] [--gather-nccl]        several GPUs behind the same cuda_impl call
 //              [--spp-per-pass P [--preview-every K] [--preview-prefix path_]]   progressive passes with previews
 #include <cstdint>
 #include <cstdio>
@@ -71,6 +72,17 @@ int main(int argc, char **argv)
             else if (a == "--depth") opt.max_depth = static_cast<std::uint32_t>(std::stoul(next()));
             else if (a == "--seed") opt.seed = std::stoull(next());
             else if (a == "--device") opt.device = std::stoi(next());
+            else if (a == "--gpus") { int n = std::stoi(next()); opt.devices.clear(); for (int d = 0; d < n; ++d) opt.devices.push_back(d); }
+            else if (a == "--devices") {
+                std::string list = next(); opt.devices.clear();
+                for (std::size_t pos = 0; pos <= list.size();) {
+                    auto comma = list.find(',', pos);
+                    if (comma == std::string::npos) comma = list.size();
+                    opt.devices.push_back(std::stoi(list.substr(pos, comma - pos)));
+                    pos = comma + 1;
+                }
+            }
+            else if (a == "--gather-nccl") opt.gather_nccl = true;
             else if (a == "--exact") opt.exact = true;
             else if (a == "--book-optics") opt.book_optics = true;
             else if (a == "--spp-per-pass") opt.samples_per_pass = static_cast<std::uint32_t>(std::stoul(next()));

@@ -141,6 +141,77 @@ class CudaTileRenderer:
         self.be.throttle(n)
 
 
+class DeviceQueueFrame:
+    """One process per GPU on the DEVICE-SIDE tile queue (include/rt_api.h): rank 0 owns the range cursors and the RGB8
+    frame; the other ranks map both through CUDA IPC (handles travel once through torch.distributed).  A frame is then
+
+        rank 0: rt_queue_dev_reset                      (stream-ordered)
+        all   : all_reduce(token)                       cursors are rewound before anyone pulls; nobody is in the previous frame
+        all   : rt_render_queue                         ONE persistent launch: the kernel takes tiles itself, steals when dry
+        all   : rt_resolve_tiles_to(rank 0's frame)     the gather: texels go straight into rank 0's memory over NVLink
+        all   : all_reduce(token)                       NCCL acknowledgement: the frame is complete on rank 0's stream
+
+    all of it queued on one CUDA stream per rank -- no host synchronisation inside a frame, no per-chunk launches."""
+
+    def __init__(self, backend, rank, world, dist, torch, stream):
+        self.be, self.rank, self.world, self.dist, self.torch, self.stream = backend, rank, world, dist, torch, stream
+        self.frame = None
+        self._frame_mapped = False
+        if rank == 0:
+            self.cursors = backend.queue_dev_create()
+            box = [backend.ipc_export(self.cursors)] if world > 1 else [None]
+        else:
+            box = [None]
+        if world > 1:
+            dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            self.cursors = backend.ipc_import(box[0])
+        self.token = torch.zeros(1, dtype=torch.int32, device=f"cuda:{backend.device}")
+
+    def map_frame(self):
+        """(Re)map rank 0's RGB8 frame; call after every rt_framebuffer on rank 0 (a resize reallocates it)."""
+        be = self.be
+        if self.rank != 0 and self._frame_mapped:
+            be.ipc_close(self.frame)
+            self._frame_mapped = False
+        if self.rank == 0:
+            ptr, _ = be.device_rgb8()
+            box = [be.ipc_export(ptr)] if self.world > 1 else [None]
+            self.frame = ptr
+        else:
+            box = [None]
+        if self.world > 1:
+            self.dist.broadcast_object_list(box, src=0)
+        if self.rank != 0:
+            self.frame = be.ipc_import(box[0])
+            self._frame_mapped = True
+
+    def _ack(self):
+        if self.world > 1:
+            with self.torch.cuda.stream(self.stream):
+                self.dist.all_reduce(self.token)
+
+    def render_frame(self, tiles, tile_w, tile_h, spp, max_depth, seed, flags=0):
+        be = self.be
+        be.clear()
+        if self.rank == 0:
+            be.queue_dev_reset(self.cursors, len(tiles), self.world)
+        self._ack()
+        be.render_queue(tiles, tile_w, tile_h, self.cursors, self.rank, self.world, spp, max_depth, seed, 0, flags)
+        be.resolve_tiles_to(self.frame)
+        self._ack()
+
+    def close(self):
+        be = self.be
+        be.sync()
+        if self.rank != 0:
+            if self._frame_mapped:
+                be.ipc_close(self.frame)
+            be.ipc_close(self.cursors)
+        else:
+            be.queue_dev_free(self.cursors)
+
+
 def device_rgb8_tensor(backend):
     """Zero-copy torch view (uint8, H*W*3) of the backend's device RGB8 buffer."""
     import torch
