@@ -55,7 +55,7 @@ enum { RT_LAMBERT = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
 enum {
     RT_FLAG_EXACT = 1u << 0,      /* parity mode: the reference's arithmetic and rejection sampler; renders are bit-identical to the
                                      oracle.  48..1024 spheres, brute force: the tensor-core kernel with parity shading
-                                     (k_render_tc<true>); otherwise, or with RT_FLAG_FILTER_FMA, the straightforward parity kernels.
+                                     (rtx::k_render_tc); otherwise, or with RT_FLAG_FILTER_FMA, the straightforward parity kernels.
                                      Without this flag the CLOSEST HIT is still the oracle's bit for bit (index, t, normal); only
                                      the shading differs (unit-ball sampling by inversion, rsqrt / reciprocal normalisations) */
     RT_FLAG_ACCEL_BRUTE = 1u << 1,/* force brute-force closest hit (spheres staged in shared memory) */
@@ -123,8 +123,8 @@ enum rt_kernel_id {
     RT_KERNEL_RENDER_PARITY = 1,     /* rtx::k_render: straightforward parity kernel, sign-mask filter on the ALU pipe */
     RT_KERNEL_RENDER_FMA = 2,        /* rtf::k_render: FMA-chain candidate filter, throughput shading */
     RT_KERNEL_RENDER_SMALL = 3,      /* rtf::k_render_small: <= 47 spheres, every sphere tested */
-    RT_KERNEL_RENDER_TC = 4,         /* rtf::k_render_tc<false>: tensor-core candidate filter, throughput shading (the timed default) */
-    RT_KERNEL_RENDER_TC_PARITY = 5,  /* rtf::k_render_tc<true>: the same kernel with the parity shading (bit-identical to the oracle) */
+    RT_KERNEL_RENDER_TC = 4,         /* rtf::k_render_tc: tensor-core candidate filter, throughput shading (the timed default) */
+    RT_KERNEL_RENDER_TC_PARITY = 5,  /* rtx::k_render_tc: the same kernel with the parity shading (bit-identical to the oracle) */
     RT_KERNEL_RENDER_BVH_PARITY = 6, /* rtx::k_render_bvh */
     RT_KERNEL_RENDER_BVH = 7         /* rtf::k_render_bvh */
 };

@@ -592,6 +592,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     if (qm) {
         if (TP % RT_BATCH != 0) return fail(RT_ERR_INVALID, "rt_render_queue: tile_w * tile_h must be a multiple of 256 (one work batch never straddles two tiles)");
         if (ntiles > kTileRing) return fail(RT_ERR_INVALID, "rt_render_queue: too many tiles");
+        if (p->flags & RT_FLAG_FILTER_CHECK) return fail(RT_ERR_INVALID, "rt_render_queue: RT_FLAG_FILTER_CHECK is a single-GPU self-check");
         const uint32_t want = ntiles + 4096u;         // tiles this GPU can acquire + the dry slots its warps touch at the end
         if (want > c->feed_slots) {
             CK(cudaStreamSynchronize(c->stream));
@@ -709,10 +710,11 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         int grid = c->sm_count * ctas;
         if ((unsigned long long)grid > want_ctas) grid = (int)want_ctas;
         if (grid < 1) grid = 1;
-        cudaError_t e = small ? rtf::launch_render_small(a, grid, st)
-                        : tensor ? (exact ? rtx::launch_render_tc(a, grid, smem, st) : rtf::launch_render_tc(a, grid, smem, st))
-                        : exact ? rtx::launch_render(a, grid, smem, st, lbvh)
-                                : rtf::launch_render(a, grid, smem, st, lbvh);
+        const bool q = qm != nullptr;
+        cudaError_t e = small ? rtf::launch_render_small(a, grid, st, q)
+                        : tensor ? (exact ? rtx::launch_render_tc(a, grid, smem, st, q) : rtf::launch_render_tc(a, grid, smem, st, q))
+                        : exact ? rtx::launch_render(a, grid, smem, st, lbvh, q)
+                                : rtf::launch_render(a, grid, smem, st, lbvh, q);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
         c->hs.last_kernel = small ? RT_KERNEL_RENDER_SMALL

@@ -33,6 +33,7 @@ struct BvhTrav {
     bool active;
 };
 
+template <bool QUEUE>
 __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
     S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
     S.ar = S.ag = S.ab = 1.f;
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     BvhTrav T;
     T.node = 0; T.sp = 0; T.best_t = FLT_MAX; T.best_i = -1; T.a = 0.f; T.ix = T.iy = T.iz = 0.f; T.active = false;
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     for (;;) {
         // ---- shade the lanes whose query finished, hand out new work, start their next query
         const bool hold = T.active;
-        shade_slot<true>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
+        shade_slot<true, QUEUE>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
         if (!hold) {
             T.best_t = FLT_MAX; T.best_i = -1;
             if (S.st == ST_ACTIVE) {

@@ -39,6 +39,16 @@ namespace RT_NS {
 
 #define RT_FULL 0xffffffffu
 
+// -DRT_DEBUG: device-side asserts on the TMEM column ranges, barrier bookkeeping, work-item / tile / feed indices and hit
+// indices (compute-sanitizer cannot attach on the GPU pool; the GPU test-suite is run once against this build instead:
+// tools/build_variant.sh debug -DRT_DEBUG=1; RTIOW_LIB=build/variants/debug/librtiow_b200.so pytest -m gpu)
+#ifdef RT_DEBUG
+#include <cassert>
+#define RT_DASSERT(x) assert(x)
+#else
+#define RT_DASSERT(x) do { } while (0)
+#endif
+
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
 
@@ -629,7 +639,9 @@ __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool l
 // A warp takes RT_BATCH consecutive work items (pixel, sample) with one atomic and deals them to the
 // lanes whose path ended, by ballot + popc prefix -- terminated paths are replaced immediately, so every
 // lane carries a live ray into the next sphere loop (compaction by regeneration).
-struct WarpPool { uint32_t next, end, tile; bool exhausted; };
+// next/end: the warp's current batch of work items.  Queue mode packs `end` as tile << 9 | items left in the batch (a batch
+// is RT_BATCH = 256 items of ONE tile), so that the device-side queue costs the render loops no extra register.
+struct WarpPool { uint32_t next, end; bool exhausted; };
 
 // ---- device-side tile queue (multi-GPU): acquire the next tile for this GPU -- own range first, then steal.
 // Range r = tiles [r T / N, (r+1) T / N) of the frame's (interleaved) tile list; cursors live in rank 0's memory.
@@ -669,44 +681,55 @@ __device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, unsign
     return v;
 }
 
-// Next batch of work items for the warp (rare: once per RT_BATCH items; kept out of line so that the queue code does not
-// cost the hot loops registers).  Returns false when there is no more work.
-#ifndef RT_POOL_REFILL_INLINE
-#define RT_POOL_REFILL_INLINE 0
+// Queue mode, lane 0: the next batch of the feed's virtual item space -> tile << 32 | first item within the tile
+// (tile >= RT_FEED_NONE: no more work).  Out of line and by value: it runs once per RT_BATCH items, and the 64-bit
+// division and the queue protocol would otherwise cost the render loops registers.
+#ifndef RT_QUEUE_NOINLINE
+#define RT_QUEUE_NOINLINE 1
 #endif
-#if RT_POOL_REFILL_INLINE
-__device__ __forceinline__
-#else
+#if RT_QUEUE_NOINLINE
 __device__ __noinline__
+#else
+__device__ __forceinline__
 #endif
-bool pool_refill(WarpPool &p, const RtRenderArgs &A)
+unsigned long long queue_next_batch(const RtRenderArgs &A)
+{
+    const unsigned long long base = atomicAdd(&A.feed->next_item, (unsigned long long)RT_BATCH);
+    const unsigned long long k = base / A.TPS;
+    const uint32_t j = (uint32_t)(base - k * A.TPS);
+    return ((unsigned long long)feed_slot_tile(A, k) << 32) | j;
+}
+
+// Next batch of work items for the warp.  Returns false when there is no more work.
+// QUEUE (template parameter of every render kernel): the work domain is the device-side tile queue instead of the
+// launch's own tile list; separate instantiations, so the single-GPU kernels carry none of the queue code.
+template <bool QUEUE>
+__device__ __forceinline__ bool pool_refill(WarpPool &p, const RtRenderArgs &A)
 {
     const uint32_t lane = threadIdx.x & 31u;
-    if (A.feed) {
-        // queue mode: a batch of the feed's virtual item space lies inside ONE slot (TPS is a multiple of RT_BATCH)
-        uint32_t t = RT_FEED_NONE, j = 0;
-        if (lane == 0) {
-            const unsigned long long base = atomicAdd(&A.feed->next_item, (unsigned long long)RT_BATCH);
-            const unsigned long long k = base / A.TPS;
-            j = (uint32_t)(base - k * A.TPS);
-            t = feed_slot_tile(A, k);
-        }
-        t = __shfl_sync(RT_FULL, t, 0);
-        j = __shfl_sync(RT_FULL, j, 0);
+    if constexpr (QUEUE) {
+        // a batch of the feed's virtual item space lies inside ONE slot (TPS is a multiple of RT_BATCH)
+        unsigned long long tj = 0ull;
+        if (lane == 0) tj = queue_next_batch(A);
+        const uint32_t t = __shfl_sync(RT_FULL, (uint32_t)(tj >> 32), 0);
+        const uint32_t j = __shfl_sync(RT_FULL, (uint32_t)tj, 0);
         if (t >= RT_FEED_NONE) return false;
-        p.next = j; p.end = j + RT_BATCH; p.tile = t;
+        RT_DASSERT(t < A.q_ntiles && t < (1u << 23) && j + RT_BATCH <= A.TPS);
+        p.next = j; p.end = (t << 9) | RT_BATCH;
+        return true;
+    } else {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(A.work_counter, RT_BATCH);
+        base = __shfl_sync(RT_FULL, base, 0);
+        if (base >= A.total_items) return false;
+        p.next = base;
+        p.end = min(base + RT_BATCH, A.total_items);
         return true;
     }
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(A.work_counter, RT_BATCH);
-    base = __shfl_sync(RT_FULL, base, 0);
-    if (base >= A.total_items) return false;
-    p.next = base;
-    p.end = min(base + RT_BATCH, A.total_items);
-    return true;
 }
 
 // Work items for the lanes that want one; `tile` = the item's tile in queue mode (items are then tile-relative).
+template <bool QUEUE>
 __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, const RtRenderArgs &A, uint32_t &tile)
 {
     const uint32_t lane = threadIdx.x & 31u;
@@ -714,15 +737,17 @@ __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, const RtRe
     uint32_t item = 0xffffffffu;
     uint32_t need = __ballot_sync(RT_FULL, want);
     while (need) {
-        if (p.next >= p.end) {
+        if (QUEUE ? (p.end & 511u) == 0u : p.next >= p.end) {
             if (p.exhausted) break;
-            if (!pool_refill(p, A)) { p.exhausted = true; break; }
+            if (!pool_refill<QUEUE>(p, A)) { p.exhausted = true; break; }
         }
-        uint32_t avail = p.end - p.next;
+        const uint32_t avail = QUEUE ? (p.end & 511u) : p.end - p.next;
         bool mine = want && item == 0xffffffffu;
         uint32_t rank = __popc(need & lt);
-        if (mine && rank < avail) { item = p.next + rank; tile = p.tile; }
-        p.next += min((uint32_t)__popc(need), avail);
+        if (mine && rank < avail) { item = p.next + rank; if (QUEUE) tile = p.end >> 9; }
+        const uint32_t adv = min((uint32_t)__popc(need), avail);
+        p.next += adv;
+        if (QUEUE) p.end -= adv;
         need = __ballot_sync(RT_FULL, want && item == 0xffffffffu);
     }
     return item;
@@ -759,7 +784,7 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // One shading pass for one path slot: finish the segment just traced (background / material), hand a new
 // camera sample to the slot if its path ended, draw the random numbers every lane needs in ONE shared
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
-template <bool LBVH, bool PAR = RT_PAR_DEFAULT>
+template <bool LBVH, bool QUEUE = false, bool PAR = RT_PAR_DEFAULT>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
                                            float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false,
                                            const float *__restrict__ s_rad = nullptr, const uint32_t *__restrict__ s_meta = nullptr,
@@ -794,6 +819,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             ++ts.capped;
             want = true;
         } else {
+            RT_DASSERT(best_i < (int)sc.n);
             float4 s = LBVH ? __ldg(sc.sph + best_i) : s_sph[best_i];
             float rad = s_rad ? s_rad[best_i] : __ldg(sc.sph_rad + best_i);
             uint32_t meta = s_meta ? s_meta[best_i] : __ldg(sc.sph_meta + best_i);
@@ -830,15 +856,16 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     uint32_t ev = S.bounce + 1u;
     for (bool need = want;;) {
         uint32_t qtile = 0u;
-        uint32_t item = pool_take(pool, need, A, qtile);
+        uint32_t item = pool_take<QUEUE>(pool, need, A, qtile);
         if (need) {
             if (item != 0xffffffffu) {
                 // item order: tile-major, then sample, then pixel -- a tile's accumulators (TP * 32 B) stay
                 // cache-resident while all of its samples are traced.  Queue mode: the item is already tile-relative.
                 uint32_t q, r, rx;
-                uint32_t tl = A.feed ? (q = item, qtile) : (A.TPS > 1u) ? div_magic(item, A.TPS, A.mTPS, q) : (q = 0u, item);
+                uint32_t tl = QUEUE ? (q = item, qtile) : (A.TPS > 1u) ? div_magic(item, A.TPS, A.mTPS, q) : (q = 0u, item);
                 uint32_t s_i = (A.TP > 1u) ? div_magic(q, A.TP, A.mTP, r) : (r = 0u, q);
                 uint4 T = A.tiles ? __ldg(A.tiles + A.t0 + tl) : A.tile0;
+                RT_DASSERT(s_i < A.spp && r < A.TP && T.x + T.z <= A.W && T.y + T.w <= A.H);
                 if (r < T.z * T.w) {                                      // edge tiles leave slots unused
                     uint32_t ty;
                     if (!A.tiles && T.z > 1u) ty = div_magic(r, T.z, A.mW0, rx);
@@ -960,7 +987,7 @@ __global__ void k_sample_ball(float *out, unsigned long long n, uint32_t key0, u
 }
 #endif
 
-template <bool LBVH, bool CHECK = false>
+template <bool LBVH, bool CHECK = false, bool QUEUE = false>
 __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -988,7 +1015,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         S[r].ox = S[r].oy = S[r].oz = 0.f; S[r].dx = S[r].dy = S[r].dz = 0.f;
         S[r].ar = S[r].ag = S[r].ab = 1.f;
     }
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     float best_t[RT_RPT]; int best_i[RT_RPT];
 #pragma unroll
@@ -998,7 +1025,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
         bool any_live = false;
 #pragma unroll
         for (int r = 0; r < RT_RPT; ++r) {
-            shade_slot<LBVH>(A, s_sph, S[r], best_t[r], best_i[r], pool, ts);
+            shade_slot<LBVH, QUEUE>(A, s_sph, S[r], best_t[r], best_i[r], pool, ts);
             any_live |= (S[r].st != ST_EMPTY);
         }
         if (!__any_sync(RT_FULL, any_live)) break;
@@ -1059,6 +1086,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3) k_render(const __grid_constant_
 #ifndef RT_SMALL_CTAS
 #define RT_SMALL_CTAS 4
 #endif
+template <bool QUEUE>
 __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(const __grid_constant__ RtRenderArgs A)
 {
     __shared__ float4 s_sph[RT_SMALL_SCENE];
@@ -1079,11 +1107,11 @@ __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(cons
     S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
     S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
     S.ar = S.ag = S.ab = 1.f;
-    WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
+    WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
     ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
     float best_t = FLT_MAX; int best_i = -1;
     for (;;) {
-        shade_slot<false>(A, s_sph, S, best_t, best_i, pool, ts, false, s_rad, s_meta, mats ? s_mat : nullptr);
+        shade_slot<false, QUEUE>(A, s_sph, S, best_t, best_i, pool, ts, false, s_rad, s_meta, mats ? s_mat : nullptr);
         if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
         best_t = FLT_MAX; best_i = -1;
         const float a = ray_a(S.dx, S.dy, S.dz);

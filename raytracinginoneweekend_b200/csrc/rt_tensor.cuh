@@ -52,14 +52,6 @@ static_assert(RT_TC_WGS * RT_TC_WGCOLS <= 512, "TMEM has 512 columns");
 static_assert(RT_TC_CHUNK % 64 == 0 && RT_TC_CHUNK >= 64 && RT_TC_CHUNK <= 256, "tile width: pairs of mask words, one MMA N");
 static_assert((1 + RT_TC_WGS * RT_TC_WGBARS) * 8 <= 448 && 452 + 4 * RT_TC_WGS <= 512, "barriers, TMEM base and done flags live in the first 512 bytes of shared memory");
 
-// -DRT_DEBUG: device-side asserts on the TMEM column ranges, barrier parities, ring indices and hit indices
-// (compute-sanitizer cannot attach on the GPU pool; the GPU test-suite is run once against this build instead)
-#ifdef RT_DEBUG
-#include <cassert>
-#define RT_DASSERT(x) assert(x)
-#else
-#define RT_DASSERT(x) do { } while (0)
-#endif
 
 namespace tc {
 
@@ -444,6 +436,8 @@ __device__ __forceinline__ void regroup(const RtRenderArgs &A, const RayWarp &r,
 
 // ---------------------------------------------------------------- the persistent bounce loop on the tensor path
 // Shading = that of the translation unit: rtf -- throughput shading (the timed default); rtx -- parity shading (RT_FLAG_EXACT).
+// QUEUE: work from the device-side tile queue (multi-GPU) instead of the launch's tile list.
+template <bool QUEUE>
 __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -475,7 +469,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
         S.st = ST_EMPTY; S.pix = 0; S.smp = 0; S.bounce = 0;
         S.ox = S.oy = S.oz = 0.f; S.dx = S.dy = S.dz = 0.f;
         S.ar = S.ag = S.ab = 1.f;
-        WarpPool pool; pool.next = 0; pool.end = 0; pool.tile = 0; pool.exhausted = false;
+        WarpPool pool; pool.next = 0; pool.end = 0; pool.exhausted = false;
         ThreadStats ts = {0, 0, 0, 0, 0, {0, 0}};
         float best_t = FLT_MAX; int best_i = -1;
 #if RT_TC_REGROUP
@@ -488,7 +482,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
 #if RT_TC_REGROUP
             tc::regroup(A, rw, s_cnt, s_x, mats_in_smem ? s_meta : nullptr, S, best_t, best_i);
 #endif
-            shade_slot<false>(A, c.s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
+            shade_slot<false, QUEUE>(A, c.s_sph, S, best_t, best_i, pool, ts, false, mats_in_smem ? s_rad : nullptr,
                                    mats_in_smem ? s_meta : nullptr, mats_in_smem ? s_mat : nullptr);
             if (!tc::wg_any(1u + rw.wg, S.st != ST_EMPTY)) {                         // whole warpgroup out of work
                 tc::ray_warp_finish(c, rw);

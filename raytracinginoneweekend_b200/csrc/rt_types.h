@@ -115,21 +115,21 @@ struct RtHitArgs {
 
 // launchers, one set per arithmetic mode (exact = --fmad=false TU, fast = FMA TU)
 namespace rtx {
-cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
-cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh);
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool queue);
+cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh, bool queue);
 cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 namespace rtf {
-cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh);
+cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh, bool queue);
 cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
 namespace rtf {
-cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool queue);
 cudaError_t launch_hits_tc(const RtHitArgs &a, int grid, size_t smem, cudaStream_t s);
-cudaError_t launch_render_small(const RtRenderArgs &a, int grid, cudaStream_t s);
+cudaError_t launch_render_small(const RtRenderArgs &a, int grid, cudaStream_t s, bool queue);
 cudaError_t small_occupancy(int *ctas_per_sm);
 cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, uint32_t key1, int lens, cudaStream_t s);
 }

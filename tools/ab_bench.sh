@@ -8,6 +8,8 @@ for round in $(seq 1 ${ROUNDS:-2}); do
     s=$(RTIOW_LIB=$d/librtiow_b200.so timeout 60 python tools/run_config.py --scene simple --spp 64 --reps 2 2>&1 | tail -1 | python -c "import sys,json; print('%.1f' % json.loads(sys.stdin.readline())['Msamples_per_s'])")
     m=$(RTIOW_LIB=$d/librtiow_b200.so timeout 90 python tools/run_config.py --scene synthetic1m --width 1920 --height 1080 --spp 8 --reps 2 2>&1 | tail -1 | python -c "import sys,json; print('%.1f' % json.loads(sys.stdin.readline())['Msamples_per_s'])")
     x=$(RTIOW_LIB=$d/librtiow_b200.so timeout 60 python tools/run_config.py --scene huge --spp 100 --reps 2 --exact 2>&1 | tail -1 | python -c "import sys,json; print('%.1f' % json.loads(sys.stdin.readline())['Msamples_per_s'])")
-    echo "round $round $n: huge $h simple $s synthetic1m $m huge-parity $x Msamples/s"
+    hq=$(RTIOW_LIB=$d/librtiow_b200.so timeout 60 python tools/run_config.py --scene huge --spp 100 --reps 2 --queue 2>&1 | tail -1 | python -c "import sys,json; print('%.1f' % json.loads(sys.stdin.readline())['Msamples_per_s'])")
+    mq=$(RTIOW_LIB=$d/librtiow_b200.so timeout 90 python tools/run_config.py --scene synthetic1m --width 1920 --height 1080 --spp 8 --reps 2 --queue 2>&1 | tail -1 | python -c "import sys,json; print('%.1f' % json.loads(sys.stdin.readline())['Msamples_per_s'])")
+    echo "round $round $n: huge $h simple $s synthetic1m $m huge-parity $x | queue mode: huge $hq synthetic1m $mq Msamples/s"
   done
 done
