@@ -91,6 +91,16 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
         raise RtError(f"{path} is missing: build it with `make -C {HERE}` (or __graft_entry__.build()); "
                       "there is no CPU fallback")
     lib = C.CDLL(path)
+    if os.environ.get("RTIOW_LIB_OLD_ABI") == "1":      # A/B timing against a library built from an older tree (tools/ab_bench.sh)
+        class _Tolerant:
+            def __init__(self, real): object.__setattr__(self, "_real", real)
+            def __getattr__(self, name):
+                try:
+                    return getattr(self._real, name)
+                except AttributeError:
+                    def missing(*a, **k): raise RtError(f"{name} is not exported by {path}")
+                    return missing
+        lib = _Tolerant(lib)
     vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int
     fp = C.POINTER(C.c_float)
     lib.rt_last_error.restype = C.c_char_p

@@ -254,7 +254,7 @@ __device__ __forceinline__ float sphere_disc(float4 s, float ox, float oy, float
 //          when even t2' + m < kMIN (both roots invalid: the sphere the path just left).  NaN / inf in the approximation
 //          make every comparison false, i.e. fall through to the IEEE evaluation.
 #ifndef RT_CAND_EARLYOUT
-#define RT_CAND_EARLYOUT 3
+#define RT_CAND_EARLYOUT 1
 #endif
 __device__ __forceinline__ bool candidate_decided(float disc, float b, float c, float a, float best_t)
 {
@@ -272,6 +272,35 @@ __device__ __forceinline__ bool candidate_decided(float disc, float b, float c, 
     }
 #endif
     return false;
+}
+
+// n / a, correctly rounded, from the correctly rounded reciprocal ra = RN(1 / a) of the ray's a, computed ONCE per ray
+// (ray_ra): two residual corrections with exact FMA residuals (Markstein: with ra = RN(1/a) and q1 faithful,
+// RN(q1 + (n - a q1) ra) = RN(n / a)).  5 dependent FMA-pipe instructions instead of the ~10 + MUFU + range check of
+// div.rn.  Verified against IEEE division on 4 x 10^8 random pairs with stressed significands (tools/check_mdiv.c: no
+// mismatch where the quotient is a normal number; a subnormal or overflowing quotient fails t > kMIN / t < best_t either
+// way).  ray_ra returns 0 outside 2^-60 < a < 2^60 -- never reached by a ray direction -- and div_by_a then divides.
+#ifndef RT_CAND_MDIV
+#define RT_CAND_MDIV 1
+#endif
+__device__ __forceinline__ float ray_ra(float a)
+{
+#if RT_CAND_MDIV && !RT_EXACT
+    return (a > 8.7e-19f && a < 1.15e18f) ? __frcp_rn(a) : 0.f;
+#else
+    return 0.f;
+#endif
+}
+__device__ __forceinline__ float div_by_a(float n, float a, float ra)
+{
+#if RT_CAND_MDIV && !RT_EXACT
+    if (ra != 0.f) {
+        const float q0 = __fmul_rn(n, ra);
+        const float q1 = __fmaf_rn(__fmaf_rn(-a, q0, n), ra, q0);
+        return __fmaf_rn(__fmaf_rn(-a, q1, n), ra, q1);
+    }
+#endif
+    return __fdiv_rn(n, a);
 }
 
 // Per-candidate reference test (src/raytracer.hxx:63-89) against the running closest hit.  Candidates are
@@ -293,20 +322,19 @@ __device__ __forceinline__ void sphere_candidate_ref(float4 s, int j, float ox, 
         }
     }
 }
-__device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz,
-                                                 float dx, float dy, float dz, float a, float &best_t, int &best_i)
+__device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz, float dx, float dy, float dz,
+                                                 float a, float ra, float &best_t, int &best_i)
 {
+    // one exit, one compare-and-select at the end: t = the root the reference would look at last, FLT_MAX if none
     float b, c;
-    float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
+    const float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
+    float t = FLT_MAX;
     if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
-        float sq = __fsqrt_rn(disc);
-        float t = __fdiv_rn(__fsub_rn(-b, sq), a);
-        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
-        else {
-            t = __fdiv_rn(__fadd_rn(-b, sq), a);
-            if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
-        }
+        const float sq = __fsqrt_rn(disc);
+        t = div_by_a(__fsub_rn(-b, sq), a, ra);
+        if (!(t < best_t && t > RT_KMIN)) t = div_by_a(__fadd_rn(-b, sq), a, ra);
     }
+    if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
 }
 
 // Brute-force closest hit for R rays per thread over the shared-memory sphere buffer.
@@ -372,7 +400,7 @@ __device__ __forceinline__ void closest_hit_brute(const float4 *__restrict__ s_s
                 int bit = __clz(cand);
                 cand &= ~(0x80000000u >> bit);
                 uint32_t j = chunk + (w << 5) + (uint32_t)bit;
-                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a[r], best_t[r], best_i[r]);
+                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a[r], 0.f, best_t[r], best_i[r]);
             }
         }
     }
@@ -447,10 +475,10 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
     if (n <= RT_SMALL_SCENE) {                       // a handful of spheres: the candidate test on each one costs less than one filter group
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const float a = ray_a(dx[r], dy[r], dz[r]);
+            const float a = ray_a(dx[r], dy[r], dz[r]), ra = ray_ra(a);
             if (live[r] && a > 0.f && a < 3.0e38f)
                 for (uint32_t j = 0; j < n; ++j)
-                    sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, best_t[r], best_i[r]);
+                    sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, ra, best_t[r], best_i[r]);
         }
         return;
     }
@@ -483,7 +511,7 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
         // one candidate per lane per iteration: the warp iterates max-over-lanes of the candidate COUNT
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const float a = ray_a(dx[r], dy[r], dz[r]);
+            const float a = ray_a(dx[r], dy[r], dz[r]), ra = ray_ra(a);
             uint32_t words = nz[r], cand = 0, w = 0;
             nz[r] = 0u;
             for (;;) {
@@ -496,7 +524,7 @@ __device__ __forceinline__ void closest_hit_brute_fast(const RtDeviceScene &sc, 
                 int lz = __clz(cand);                        // bit 23 (lz = 8) is the first sphere of the group
                 cand &= ~(0x80000000u >> lz);
                 uint32_t j = chunk + w * RT_FGROUP + (uint32_t)(lz - 8);
-                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, best_t[r], best_i[r]);
+                if (j < n) sphere_candidate(s_sph[j], (int)j, ox[r], oy[r], oz[r], dx[r], dy[r], dz[r], a, ra, best_t[r], best_i[r]);
             }
         }
     }
@@ -526,10 +554,11 @@ __device__ __forceinline__ void bvh_leaf_sphere(const RtDeviceScene &sc, uint32_
     float b, c;
     float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
     if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
+        const float ra = ray_ra(a);
         float sq = __fsqrt_rn(disc);
-        float t = __fdiv_rn(__fsub_rn(-b, sq), a);
+        float t = div_by_a(__fsub_rn(-b, sq), a, ra);
         bool ok = t < FLT_MAX && t > RT_KMIN;
-        if (!ok) { t = __fdiv_rn(__fadd_rn(-b, sq), a); ok = t < FLT_MAX && t > RT_KMIN; }
+        if (!ok) { t = div_by_a(__fadd_rn(-b, sq), a, ra); ok = t < FLT_MAX && t > RT_KMIN; }
         if (ok && t <= best_t) {
             const int j = (int)__ldg(sc.bvh_prims + pos);
             if (t < best_t || j < best_i) { best_t = t; best_i = j; }
@@ -682,10 +711,9 @@ __device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, unsign
 }
 
 // Queue mode, lane 0: the next batch of the feed's virtual item space -> tile << 32 | first item within the tile
-// (tile >= RT_FEED_NONE: no more work).  Out of line and by value: it runs once per RT_BATCH items, and the 64-bit
-// division and the queue protocol would otherwise cost the render loops registers.
+// (tile >= RT_FEED_NONE: no more work).
 #ifndef RT_QUEUE_NOINLINE
-#define RT_QUEUE_NOINLINE 1
+#define RT_QUEUE_NOINLINE 0    // measured (huge scene through the queue, 1 GPU): inline 1.60, out of line 1.41 Gsamples/s
 #endif
 #if RT_QUEUE_NOINLINE
 __device__ __noinline__
@@ -823,7 +851,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             float4 s = LBVH ? __ldg(sc.sph + best_i) : s_sph[best_i];
             float rad = s_rad ? s_rad[best_i] : __ldg(sc.sph_rad + best_i);
             uint32_t meta = s_meta ? s_meta[best_i] : __ldg(sc.sph_meta + best_i);
-            m = s_mat ? s_mat[meta & 0x3fffffffu] : __ldg(sc.mat + (meta & 0x3fffffffu));
+            m = s_mat ? s_mat[meta & 0x3fffffffu] : LBVH ? __ldg(sc.sph_mat + best_i) : __ldg(sc.mat + (meta & 0x3fffffffu));
             kind = (int)(meta >> 30);
             p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
             if constexpr (PAR) {
@@ -1114,10 +1142,10 @@ __global__ void __launch_bounds__(RT_THREADS, RT_SMALL_CTAS) k_render_small(cons
         shade_slot<false, QUEUE>(A, s_sph, S, best_t, best_i, pool, ts, false, s_rad, s_meta, mats ? s_mat : nullptr);
         if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
         best_t = FLT_MAX; best_i = -1;
-        const float a = ray_a(S.dx, S.dy, S.dz);
+        const float a = ray_a(S.dx, S.dy, S.dz), ra = ray_ra(a);
         if (S.st == ST_ACTIVE && a > 0.f && a < 3.0e38f) {
             for (uint32_t j = 0; j < n; ++j)
-                sphere_candidate(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, best_t, best_i);
+                sphere_candidate(s_sph[j], (int)j, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, a, ra, best_t, best_i);
         }
     }
     uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};

@@ -27,6 +27,8 @@ struct RtDeviceScene {
     const float *sph_rad;
     const uint32_t *sph_meta;
     const float4 *mat;
+    const float4 *sph_mat;       // float4[npad]: the material record of each sphere, mat[sph_meta & 0x3fffffff] copied out per sphere
+                                 // (LBVH shading: one independent load instead of the dependent index -> material round trip)
     uint32_t n, npad;
     uint32_t m;                  // materials
     // conservative candidate filter of the throughput build (see rt_device.cuh, closest_hit_brute_fast)
