@@ -428,11 +428,34 @@ class _CtxView(Backend):
         self.ctx = None
 
 
+def _preload_bundled_nccl():
+    """rt_multi dlopen()s "libnccl.so.2".  In a Python process that also imports torch, the library of that SONAME must be the
+    one torch was built against (its wheel bundles a newer NCCL than the system's: loading the system one first makes a
+    later `import torch` fail on a missing symbol).  So load the bundled library first, globally, when there is one."""
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    if spec is None or not spec.submodule_search_locations:
+        return None
+    for base in spec.submodule_search_locations:
+        cand = os.path.join(base, "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            try:
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                return cand
+            except OSError:
+                return None
+    return None
+
+
 class MultiBackend:
     """rt_multi: several GPUs of ONE process behind one call (device-side tile queue, peer-store gather, NCCL ack)."""
     GATHER_NCCL = 1
 
     def __init__(self, devices):
+        _preload_bundled_nccl()
         self.lib = load_library()
         self.devices = [int(d) for d in devices]
         arr = (C.c_int * len(self.devices))(*self.devices)

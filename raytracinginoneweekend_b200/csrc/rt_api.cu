@@ -56,7 +56,6 @@ struct rt_ctx {
 
     // scene
     float4 *d_sph = nullptr; float *d_rad = nullptr; uint32_t *d_meta = nullptr; float4 *d_mat = nullptr;
-    float4 *d_smat = nullptr;               // per-sphere copy of the material records (LBVH shading)
     float4 *d_filt = nullptr;               // conservative-filter records of the throughput build
     float4 *d_tcb = nullptr;                // tensor-filter sphere matrix (rt_tensor.cuh), nullptr above RT_TC_MAX_SPHERES
     uint32_t tc_ns = 0;
@@ -178,7 +177,6 @@ int get_events(rt_ctx *c, EventPair *out)
 void free_scene(rt_ctx *c)
 {
     cudaFree(c->d_sph); cudaFree(c->d_rad); cudaFree(c->d_meta); cudaFree(c->d_mat); cudaFree(c->d_filt); cudaFree(c->d_tcb);
-    cudaFree(c->d_smat); c->d_smat = nullptr;
     c->d_tcb = nullptr; c->tc_ns = 0;
     c->d_sph = nullptr; c->d_rad = nullptr; c->d_meta = nullptr; c->d_mat = nullptr; c->d_filt = nullptr;
     c->n = c->npad = c->m = c->nfilt = 0;
@@ -195,7 +193,7 @@ void free_framebuffer(rt_ctx *c)
 RtDeviceScene device_scene(const rt_ctx *c, bool lbvh)
 {
     RtDeviceScene s{};
-    s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat; s.sph_mat = c->d_smat;
+    s.sph = c->d_sph; s.sph_rad = c->d_rad; s.sph_meta = c->d_meta; s.mat = c->d_mat;
     s.n = c->n; s.npad = c->npad; s.m = c->m;
     s.filt = c->d_filt; s.nfilt = c->nfilt; s.sigma = c->sigma; s.S = c->S; s.o_limit2 = c->o_limit2;
     s.tc_b = c->d_tcb; s.tc_ns = c->tc_ns; s.tc_gx = c->tc_g[0]; s.tc_gy = c->tc_g[1]; s.tc_gz = c->tc_g[2];
@@ -387,7 +385,6 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         CK(cudaMalloc(&c->d_rad, (size_t)npad * sizeof(float)));
         CK(cudaMalloc(&c->d_meta, (size_t)npad * sizeof(uint32_t)));
         CK(cudaMalloc(&c->d_mat, (size_t)m * sizeof(float4)));
-        CK(cudaMalloc(&c->d_smat, (size_t)npad * sizeof(float4)));
         CK(cudaMalloc(&c->d_filt, (size_t)((n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP) * sizeof(float4)));
     }
     const uint32_t nfilt = (n + RT_FGROUP - 1) / RT_FGROUP * RT_FGROUP;
@@ -400,8 +397,8 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         c->tc_ns = tc_ns;
     }
     size_t b_sph = (size_t)npad * 16, b_rad = (size_t)npad * 4, b_meta = (size_t)npad * 4, b_mat = (size_t)m * 16;
-    size_t b_filt = (size_t)nfilt * 16, b_tcb = (size_t)tc_ns * 8 * 16, b_smat = (size_t)npad * 16;
-    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat + b_filt + b_tcb + b_smat);
+    size_t b_filt = (size_t)nfilt * 16, b_tcb = (size_t)tc_ns * 8 * 16;
+    int r = ensure_pinned(c, b_sph + b_rad + b_meta + b_mat + b_filt + b_tcb);
     if (r) return r;
     CK(cudaStreamSynchronize(c->stream));   // staging buffer may still be in flight
     char *h = (char *)c->h_pin;
@@ -446,9 +443,6 @@ int rt_scene_upload(rt_ctx *c, const rt_sphere *spheres, uint32_t n, const rt_ma
         }
     }
     for (uint32_t i = 0; i < m; ++i) hmat[i] = make_float4(materials[i].r, materials[i].g, materials[i].b, materials[i].param);
-    float4 *hsm = (float4 *)(h + b_sph + b_rad + b_meta + b_mat + b_filt + b_tcb);
-    for (uint32_t i = 0; i < npad; ++i) hsm[i] = hmat[i < n ? spheres[i].mat : 0u];
-    CK(cudaMemcpyAsync(c->d_smat, hsm, b_smat, cudaMemcpyHostToDevice, c->stream));
     if (tc_ns) {
         // Sphere side of the bilinear form of rt_tensor.cuh, expanded about g = the component-wise median of the
         // centres (keeps |c - g| small for the many small spheres whatever the ground sphere does).

@@ -325,9 +325,13 @@ __device__ __forceinline__ void sphere_candidate_ref(float4 s, int j, float ox, 
 __device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, float oy, float oz, float dx, float dy, float dz,
                                                  float a, float ra, float &best_t, int &best_i)
 {
-    // one exit, one compare-and-select at the end: t = the root the reference would look at last, FLT_MAX if none
+#ifndef RT_CAND_SINGLE_EXIT
+#define RT_CAND_SINGLE_EXIT 1
+#endif
     float b, c;
     const float disc = sphere_disc(s, ox, oy, oz, dx, dy, dz, a, b, c);
+#if RT_CAND_SINGLE_EXIT
+    // one exit, one compare-and-select at the end: t = the root the reference would look at last, FLT_MAX if none
     float t = FLT_MAX;
     if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
         const float sq = __fsqrt_rn(disc);
@@ -335,6 +339,17 @@ __device__ __forceinline__ void sphere_candidate(float4 s, int j, float ox, floa
         if (!(t < best_t && t > RT_KMIN)) t = div_by_a(__fadd_rn(-b, sq), a, ra);
     }
     if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+#else
+    if (disc > 0.f && !candidate_decided(disc, b, c, a, best_t)) {
+        float sq = __fsqrt_rn(disc);
+        float t = div_by_a(__fsub_rn(-b, sq), a, ra);
+        if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        else {
+            t = div_by_a(__fadd_rn(-b, sq), a, ra);
+            if (t < best_t && t > RT_KMIN) { best_t = t; best_i = j; }
+        }
+    }
+#endif
 }
 
 // Brute-force closest hit for R rays per thread over the shared-memory sphere buffer.
@@ -851,7 +866,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
             float4 s = LBVH ? __ldg(sc.sph + best_i) : s_sph[best_i];
             float rad = s_rad ? s_rad[best_i] : __ldg(sc.sph_rad + best_i);
             uint32_t meta = s_meta ? s_meta[best_i] : __ldg(sc.sph_meta + best_i);
-            m = s_mat ? s_mat[meta & 0x3fffffffu] : LBVH ? __ldg(sc.sph_mat + best_i) : __ldg(sc.mat + (meta & 0x3fffffffu));
+            m = s_mat ? s_mat[meta & 0x3fffffffu] : __ldg(sc.mat + (meta & 0x3fffffffu));
             kind = (int)(meta >> 30);
             p = mk3(S.ox + S.dx * best_t, S.oy + S.dy * best_t, S.oz + S.dz * best_t);   // ray::point_at
             if constexpr (PAR) {

@@ -301,10 +301,9 @@ __device__ __forceinline__ void ray_warp_finish(const Cta &c, const RayWarp &r)
 // THE closest hit of the tensor path: this thread's ray against all spheres.  Must be called by all four warps of the
 // warpgroup in every pass (idle slots pass live = false).  Returns the oracle's hit: smallest t in (kMIN, FLT_MAX) of the
 // IEEE reference test, ties to the lowest sphere index (src/raytracer.hxx:52-118).
-template <bool CHECK>
 __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDeviceScene &sc, bool live,
                                             float ox, float oy, float oz, float dx, float dy, float dz,
-                                            float &best_t, int &best_i, unsigned long long *stats)
+                                            float &best_t, int &best_i, bool check, unsigned long long *stats)
 {
     {
         float row[32];
@@ -317,8 +316,16 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
     }
     uint32_t nz = 0u;                       // bit (31 - w): mask word w is non-empty
     best_t = FLT_MAX; best_i = -1;
+#ifndef RT_TC_RA_LATE
+#define RT_TC_RA_LATE 0
+#endif
     const float a = ray_a(dx, dy, dz);                      // src/raytracer.hxx:56, the reference's operation order
+#if !RT_TC_RA_LATE
     const float ra = ray_ra(a);
+#endif
+#if RT_TC_UNROLL1
+#pragma unroll 1
+#endif
     for (uint32_t t = 0; t < c.nch; ++t) {
         const uint32_t b = t % RT_TC_NBUF;
         bar_wait(r.bar + 1 + b, (r.full_parity >> b) & 1u);
@@ -354,6 +361,9 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
         }
     }
     // pass 2: the reference test on this lane's candidates, increasing sphere index, strict <
+#if RT_TC_RA_LATE
+    const float ra = ray_ra(a);
+#endif
     uint32_t words = live ? nz : 0u, cand = 0u, w = 0u;
     for (;;) {
         if (cand == 0u) {
@@ -368,7 +378,11 @@ __device__ __forceinline__ void closest_hit(const Cta &c, RayWarp &r, const RtDe
         if (j < c.n) sphere_candidate(c.s_sph[j], (int)j, ox, oy, oz, dx, dy, dz, a, ra, best_t, best_i);
     }
     RT_DASSERT(best_i < (int)c.n);
-    if (CHECK && live) {                    // self-check (RT_FLAG_FILTER_CHECK, its own instantiation): the plain test over all spheres must agree
+    // self-check (RT_FLAG_FILTER_CHECK): the plain test over all spheres must agree.  A RUNTIME flag on purpose: with the
+    // check compiled out of the timed instantiation (a template parameter) the same kernel ran at 1.16 instead of 1.71
+    // Gsamples/s (run 5 of round 2, same box, same sources otherwise: profiles/r02_ab5.log) -- a code generation effect
+    // of ptxas on this 4 000-instruction kernel, not of the check, which never executes in a timed run.
+    if (check && live) {
         float ct = FLT_MAX; int ci = -1;
         for (uint32_t j = 0; j < c.n; ++j)
             sphere_candidate_ref(c.s_sph[j], (int)j, ox, oy, oz, dx, dy, dz, a, ct, ci);
@@ -438,8 +452,8 @@ __device__ __forceinline__ void regroup(const RtRenderArgs &A, const RayWarp &r,
 
 // ---------------------------------------------------------------- the persistent bounce loop on the tensor path
 // Shading = that of the translation unit: rtf -- throughput shading (the timed default); rtx -- parity shading (RT_FLAG_EXACT).
-// QUEUE: work from the device-side tile queue instead of the launch's tile list.  CHECK: RT_FLAG_FILTER_CHECK.
-template <bool QUEUE, bool CHECK = false>
+// QUEUE: work from the device-side tile queue instead of the launch's tile list.
+template <bool QUEUE>
 __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_constant__ RtRenderArgs A)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -490,7 +504,8 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_render_tc(const __grid_con
                 tc::ray_warp_finish(c, rw);
                 break;
             }
-            tc::closest_hit<CHECK>(c, rw, A.sc, S.st == ST_ACTIVE, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, best_t, best_i, A.stats);
+            tc::closest_hit(c, rw, A.sc, S.st == ST_ACTIVE, S.ox, S.oy, S.oz, S.dx, S.dy, S.dz, best_t, best_i,
+                            A.check != 0u, A.stats);
         }
         uint32_t v[5] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped};
 #pragma unroll
@@ -537,7 +552,7 @@ __global__ void __launch_bounds__(RT_TC_THREADS, 1) k_hits_tc(const __grid_const
             float ox = 0.f, oy = 0.f, oz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
             if (live) hits_ray(A, i, ox, oy, oz, dx, dy, dz);
             float bt; int bi;
-            tc::closest_hit<false>(c, rw, A.sc, live, ox, oy, oz, dx, dy, dz, bt, bi, A.stats);
+            tc::closest_hit(c, rw, A.sc, live, ox, oy, oz, dx, dy, dz, bt, bi, false, A.stats);
             if (live) hits_store(A, i, bi, bt, bi >= 0 ? c.s_sph[bi] : make_float4(0.f, 0.f, 0.f, 0.f), ox, oy, oz, dx, dy, dz);
         }
     }

@@ -27,8 +27,6 @@ struct RtDeviceScene {
     const float *sph_rad;
     const uint32_t *sph_meta;
     const float4 *mat;
-    const float4 *sph_mat;       // float4[npad]: the material record of each sphere, mat[sph_meta & 0x3fffffff] copied out per sphere
-                                 // (LBVH shading: one independent load instead of the dependent index -> material round trip)
     uint32_t n, npad;
     uint32_t m;                  // materials
     // conservative candidate filter of the throughput build (see rt_device.cuh, closest_hit_brute_fast)
@@ -162,6 +160,9 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #endif
 #ifndef RT_TC_REGROUP
 #define RT_TC_REGROUP 0            // 1: material-regrouping prototype (north_star (3)): sort the 128 paths of a warpgroup by shading kind
+#endif
+#ifndef RT_TC_UNROLL1
+#define RT_TC_UNROLL1 0            // 1: do not unroll the ray warps' tile loop (measurement option)
 #endif
 #ifndef RT_TC_RAY_HINT
 #define RT_TC_RAY_HINT 0           // > 0: suspend-time hint (ns) of the ray warps' try_wait on an accumulator tile; 0 = bare spin

@@ -47,7 +47,7 @@ def test_device_queue_on_one_gpu_equals_plain_render(be):
             assert_bits_equal(be.readback_accum(), want, f"accumulators through the device queue, flags {flags}")
             assert np.array_equal(be.copy_rgb8(), want_img)
         with pytest.raises(RtError, match="multiple of 256"):
-            be.render_queue(tiles, 30, 8, cur, 0, 1, spp)
+            be.render_queue(tiles, 32, 12, cur, 0, 1, spp)
     finally:
         be.queue_dev_free(cur)
 

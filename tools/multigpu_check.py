@@ -55,7 +55,14 @@ all_counts = [torch.zeros_like(counts) for _ in range(world)]
 dist.all_gather(all_counts, counts)
 if rank == 0:
     multi = frame.cpu().numpy().reshape(H, W, 3).copy()
-    be.clear(); be.render(spp, 50, seed=1); single = be.readback_rgb8()
+    # the single-GPU frame through the same kernel instantiation (the shading is compiled with FMA contraction, so the
+    # tile-list and the tile-queue instantiations may differ in the last bit of a radiance sample)
+    be.clear()
+    if mode == "device":
+        be.render(spp, 50, seed=1)
+    else:
+        be.render_tiles(tiles, 128, 64, spp, 50, seed=1)
+    single = be.readback_rgb8()
     print(json.dumps({"mode": mode, "world": world, "W": W, "H": H, "spp": spp, "identical_to_single_gpu": bool(np.array_equal(multi, single)),
                       "tiles_per_rank": [int(c[0]) for c in all_counts], "stolen_per_rank": [int(c[1]) for c in all_counts],
                       "seconds": times, "Gsamples_per_s": W * H * spp / min(times) / 1e9}), flush=True)
