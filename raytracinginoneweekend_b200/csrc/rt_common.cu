@@ -99,7 +99,7 @@ __global__ void k_resolve(const unsigned long long *__restrict__ accum, unsigned
 __global__ void k_queue_reset(uint32_t *cursors, uint32_t ntiles, uint32_t nranks)
 {
     const uint32_t r = threadIdx.x;
-    if (r < nranks) cursors[r * RT_QUEUE_STRIDE] = (uint32_t)(((unsigned long long)r * ntiles) / nranks);
+    if (r < nranks) cursors[r * RT_QUEUE_STRIDE] = (r * ntiles) / nranks;      // ntiles <= 2^16, nranks <= 64
 }
 // count += spp on every pixel of the tiles this GPU acquired (the feed's slot table, read after the render kernel)
 __global__ void k_add_count_feed(unsigned long long *accum, uint32_t W, const uint4 *tiles, const uint32_t *slots,

@@ -689,12 +689,20 @@ struct WarpPool { uint32_t next, end; bool exhausted; };
 
 // ---- device-side tile queue (multi-GPU): acquire the next tile for this GPU -- own range first, then steal.
 // Range r = tiles [r T / N, (r+1) T / N) of the frame's (interleaved) tile list; cursors live in rank 0's memory.
-__device__ __forceinline__ uint32_t queue_fetch(const RtRenderArgs &A)
+#ifndef RT_QUEUE_FETCH_NOINLINE
+#define RT_QUEUE_FETCH_NOINLINE 0    // measured (1M-sphere LBVH through the queue, 256 spp): inline 853, out of line 806 Msamples/s (tile-list order: 890)
+#endif
+#if RT_QUEUE_FETCH_NOINLINE
+__device__ __noinline__             // once per tile: kept out of the render loops
+#else
+__device__ __forceinline__
+#endif
+uint32_t queue_fetch(const RtRenderArgs &A)
 {
     if (*reinterpret_cast<volatile uint32_t *>(&A.feed->drained)) return RT_FEED_NONE;
     for (uint32_t d = 0; d < A.q_nranks; ++d) {
         const uint32_t v = (A.q_rank + d) % A.q_nranks;
-        const uint32_t hi = (uint32_t)(((unsigned long long)(v + 1u) * A.q_ntiles) / A.q_nranks);
+        const uint32_t hi = ((v + 1u) * A.q_ntiles) / A.q_nranks;          // ntiles <= 2^16, nranks <= 64: 32 bits are enough
         uint32_t *cur = A.q_cursors + v * RT_QUEUE_STRIDE;
         if (d > 0u && *reinterpret_cast<volatile uint32_t *>(cur) >= hi) continue;     // a dry victim: do not bump it again
         const uint32_t t = atomicAdd_system(cur, 1u);
@@ -704,9 +712,8 @@ __device__ __forceinline__ uint32_t queue_fetch(const RtRenderArgs &A)
     return RT_FEED_NONE;
 }
 // tile of feed slot k (called by ONE lane): the first warp to reach a slot talks to the queue, the others wait for it
-__device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, unsigned long long k)
+__device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, uint32_t k)
 {
-    if (k >= A.feed_slots) return RT_FEED_NONE;
     uint32_t *slot = A.feed->slot + k;
     uint32_t v = *reinterpret_cast<volatile uint32_t *>(slot);
     if (v == RT_FEED_EMPTY) {
@@ -725,22 +732,19 @@ __device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, unsign
     return v;
 }
 
-// Queue mode, lane 0: the next batch of the feed's virtual item space -> tile << 32 | first item within the tile
-// (tile >= RT_FEED_NONE: no more work).
-#ifndef RT_QUEUE_NOINLINE
-#define RT_QUEUE_NOINLINE 0    // measured (huge scene through the queue, 1 GPU): inline 1.60, out of line 1.41 Gsamples/s
-#endif
-#if RT_QUEUE_NOINLINE
-__device__ __noinline__
-#else
-__device__ __forceinline__
-#endif
-unsigned long long queue_next_batch(const RtRenderArgs &A)
+// Queue mode, lane 0: the next batch of work -> tile << 32 | first item within the tile (tile >= RT_FEED_NONE: no more work).
+// Slots are opened in order, so a dry slot means that everything behind it is dry too.
+__device__ __forceinline__ unsigned long long queue_next_batch(const RtRenderArgs &A)
 {
-    const unsigned long long base = atomicAdd(&A.feed->next_item, (unsigned long long)RT_BATCH);
-    const unsigned long long k = base / A.TPS;
-    const uint32_t j = (uint32_t)(base - k * A.TPS);
-    return ((unsigned long long)feed_slot_tile(A, k) << 32) | j;
+    uint32_t *ctr = A.feed->slot + A.feed_slots;
+    for (;;) {
+        const uint32_t k = *reinterpret_cast<volatile uint32_t *>(&A.feed->cur);
+        const uint32_t t = (k < A.feed_slots) ? feed_slot_tile(A, k) : RT_FEED_NONE;
+        if (t >= RT_FEED_NONE) return (unsigned long long)RT_FEED_NONE << 32;
+        const uint32_t j = atomicAdd(ctr + k, RT_BATCH);
+        if (j < A.TPS) return ((unsigned long long)t << 32) | j;
+        atomicCAS(&A.feed->cur, k, k + 1u);                 // this tile is handed out completely: open the next slot
+    }
 }
 
 // Next batch of work items for the warp.  Returns false when there is no more work.
@@ -751,7 +755,7 @@ __device__ __forceinline__ bool pool_refill(WarpPool &p, const RtRenderArgs &A)
 {
     const uint32_t lane = threadIdx.x & 31u;
     if constexpr (QUEUE) {
-        // a batch of the feed's virtual item space lies inside ONE slot (TPS is a multiple of RT_BATCH)
+        // a batch lies inside ONE tile (TPS is a multiple of RT_BATCH)
         unsigned long long tj = 0ull;
         if (lane == 0) tj = queue_next_batch(A);
         const uint32_t t = __shfl_sync(RT_FULL, (uint32_t)(tj >> 32), 0);

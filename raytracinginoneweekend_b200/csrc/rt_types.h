@@ -60,18 +60,20 @@ struct RtDeviceCamera {          // src/camera.hxx:66-76 derived state
 // Device-side tile queue (multi-GPU).  The frame's tile list is split into one contiguous range per rank;
 // the cursor of range r lives in RANK 0's memory (peer-mapped over NVLink: cudaDeviceEnablePeerAccess or CUDA IPC), one
 // 64-byte line each.  A persistent render kernel acquires tiles itself: own range first (atomicAdd at system scope on
-// its cursor), then it steals by advancing another range's cursor.  Locally the kernel keeps a FEED: a 64-bit item
-// counter over the virtual concatenation of the tiles this GPU acquired (slot k = the k-th acquired tile, TPS items
-// each) and the table slot -> tile, filled on demand by the first warp that reaches a slot.
+// its cursor), then it steals by advancing another range's cursor.  Locally the kernel keeps a FEED: the tiles this GPU
+// acquired, in order (slot k = the k-th acquired tile, filled on demand by the first warp that reaches it), one 32-bit
+// item counter per slot (TPS = tile pixels x spp items each, handed out in batches of RT_BATCH) and the index of the
+// slot currently being handed out.  All 32-bit, no division: the render loops pay two local atomics per 256 items.
 #define RT_FEED_EMPTY 0xffffffffu      // slot not acquired yet
 #define RT_FEED_FETCHING 0xfffffffeu   // a warp is talking to the queue for this slot
 #define RT_FEED_NONE 0xfffffffdu       // the queue was dry: no more tiles for this GPU
 #define RT_QUEUE_STRIDE 16u            // cursor r is at cursors[r * RT_QUEUE_STRIDE] (uint32, one 64-byte line each)
 struct RtTileFeed {
-    unsigned long long next_item;      // zeroed before the launch
+    uint32_t cur;                      // slot being handed out; zeroed before the launch
     uint32_t drained;                  // set once a fetch found every range dry
-    uint32_t pad;
+    uint32_t pad[2];
     uint32_t slot[1];                  // [nslots] RT_FEED_EMPTY before the launch; afterwards the tiles this GPU rendered
+                                       // followed by ctr[nslots]: items handed out of each slot, zeroed before the launch
 };
 
 struct RtRenderArgs {
