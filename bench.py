@@ -292,6 +292,7 @@ def run_gpu_arm(args):
         elif world > 1:
             sched = multigpu.StealingScheduler(queue, rank, world, len(tiles))
             renderer = multigpu.CudaTileRenderer(be, TILE_W, TILE_H, spp, DEPTH, SEED, flags)
+        phase_trace = []
         r_start = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         r_end = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
 
@@ -301,7 +302,7 @@ def run_gpu_arm(args):
             if dq is not None:                # ONE persistent launch per GPU: tiles pulled from the device-side queue,
                 if i is not None:             # texels stored into rank 0's frame, NCCL all-reduce as the acknowledgement
                     r_start[i].record(stream)
-                dq.render_frame(tiles, TILE_W, TILE_H, spp, DEPTH, SEED, flags)
+                dq.render_frame(tiles, TILE_W, TILE_H, spp, DEPTH, SEED, flags, trace=(phase_trace if i == steps - 1 else None))
                 if i is not None:
                     r_end[i].record(stream)
                 return
@@ -388,7 +389,8 @@ def run_gpu_arm(args):
         work = torch.tensor([st["samples"], st["segments"], st["launches"], st["node_visits"], st["sphere_tests"]],
                             dtype=torch.float64, device=dev)
         own_tiles = be.tiles_rendered() if dq is not None else (sched.own_taken if sched else 0)
-        mine = torch.tensor([dev_ms, render_ms, float(own_tiles), float(sched.stolen if sched else 0)],
+        ph = [phase_trace[k].elapsed_time(phase_trace[k + 1]) for k in range(4)] if len(phase_trace) == 5 else [0.0] * 4
+        mine = torch.tensor([dev_ms, render_ms, float(own_tiles), float(sched.stolen if sched else 0)] + ph,
                             dtype=torch.float64, device=dev)
         per_rank = [torch.zeros_like(mine) for _ in range(world)] if world > 1 else [mine]
         if world > 1:
@@ -406,7 +408,9 @@ def run_gpu_arm(args):
             "sphere_tests": sphere_tests, "stats_rank0": st, "kernel": KERNEL_NAMES.get(st["last_kernel"], "?"),
             "frame_sha256": frame_hash,
             "ranks": [{"rank": i, "step_ms": float(v[0]) / steps, "render_phase_ms": float(v[1]) / steps,
-                       "tiles_last_step": int(v[2]), "stolen_tiles_last_step": int(v[3])} for i, v in enumerate(per_rank)],
+                       "tiles_last_step": int(v[2]), "stolen_tiles_last_step": int(v[3]),
+                       "phases_ms_last_step": {"clear+ack": float(v[4]), "render": float(v[5]), "resolve_to_rank0": float(v[6]),
+                                               "ack": float(v[7])}} for i, v in enumerate(per_rank)],
         }
         if e2e:
             res["e2e"] = {"value": float(W) * H * spp * e2e["steps"] / (e2e_ms * 1e-3) / 1e9, "unit": UNIT,
@@ -456,19 +460,25 @@ def run_gpu_arm(args):
                             "the FMA pipe could execute)",
                     "fp32_algorithmic": fp32_model, "ms_per_launch": ms, "rank": 0}
         if st["node_visits"] > 0:
-            # LBVH: the tree is L2/L1 resident (DRAM traffic ~1 GB per launch), so HBM is not the bound; the kernel is
-            # issue bound.  Reported: requested node/leaf bytes per second (SURVEY 8(d)'s byte model at 64 B per two-box
-            # node) against the measured HBM copy bandwidth for continuity -- a figure above 1 only says "served by cache".
+            # LBVH.  HBM is NOT what bounds this kernel, and the line says so with the honest figure: the bytes that MUST come
+            # from DRAM once per launch (the tree: (n-1) nodes x 64 B, the sphere records: n x 28 B, the accumulators: W*H*32 B)
+            # against the measured HBM copy bandwidth -- a fraction of a per cent.  The SMs REQUEST node_visits x 64 B + leaf
+            # tests x 16 B (SURVEY 8(d)'s model, 7-8 TB/s here), served by L1/L2 (ncu: L2 hit rate 87 %, DRAM ~30 GB/s); the limiter
+            # is issue slots (ncu: 71 % issue-active, 15 of 32 lanes per instruction; profiles/r01_ncu_k_render_bvh_center.json).
             hbm = float(measured_peaks().get("hbm_gbs", 0) or 0)
             peak_src = "MEASURED_PEAKS.json hbm_gbs" if hbm else "fallback 6550 GB/s (B200_PROFILING.md)"
             hbm = hbm or 6550.0
-            nbytes = (st["node_visits"] * 64.0 + st["sphere_tests"] * 16.0) / steps
-            ach = nbytes / (ms * 1e-3) / 1e9
+            compulsory = (sc.n - 1) * 64.0 + sc.n * 28.0 + W * H * 32.0
+            ach = compulsory / (ms * 1e-3) / 1e9
+            requested = (st["node_visits"] * 64.0 + st["sphere_tests"] * 16.0) / steps
             return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
                     "kernel": f"{kernel} (persistent bounce loop, resumable LBVH traversal, stacks in shared memory)",
-                    "peak_source": peak_src, "byte_model": "node_visits * 64 B + leaf_tests * 16 B (device counters)",
-                    "note": "requested bytes, served mostly by L1/L2 (ncu: DRAM ~30 GB/s); the real bound is issue slots -- see "
-                            "profiles/ and DESIGN section 6",
+                    "peak_source": peak_src,
+                    "byte_model": "compulsory DRAM bytes per launch: (n-1) nodes * 64 B + n sphere records * 28 B + W*H*32 B of accumulators",
+                    "note": "not HBM bound (frac << 1 on purpose): the tree is L2-resident; the kernel is issue bound -- 71 % issue-active at "
+                            "15 of 32 lanes (ncu, profiles/r01_ncu_k_render_bvh_center.json)",
+                    "l2_request_model": {"bytes_per_launch": requested, "GBps": requested / (ms * 1e-3) / 1e9,
+                                         "model": "node_visits * 64 B + leaf_tests * 16 B (device counters): what the SMs request, served by L1/L2"},
                     "node_visits_per_segment": st["node_visits"] / max(1, st["segments"]),
                     "leaf_tests_per_segment": st["sphere_tests"] / max(1, st["segments"]),
                     "ms_per_launch": ms, "rank": 0}

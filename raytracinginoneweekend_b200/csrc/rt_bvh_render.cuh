@@ -21,6 +21,9 @@
 #define RT_BVH_STEPS 2              // node steps between two exit votes
 #endif
 #define RT_BVH_OVF_DEPTH 64
+#ifndef RT_BVH_BATCH
+#define RT_BVH_BATCH 32u            // work items a warp takes at once (see pool_refill: heavy-tailed path cost)
+#endif
 #ifndef RT_BVH_BRANCHFREE
 #define RT_BVH_BRANCHFREE 0        // 1: push / pop as single predicated shared-memory instructions (measured slower: 795 vs 809 Msamples/s on 1M spheres)
 #endif
@@ -57,7 +60,7 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     for (;;) {
         // ---- shade the lanes whose query finished, hand out new work, start their next query
         const bool hold = T.active;
-        shade_slot<true, QUEUE>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
+        shade_slot<true, QUEUE, RT_PAR_DEFAULT, RT_BVH_BATCH>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
         if (!hold) {
             T.best_t = FLT_MAX; T.best_i = -1;
             if (S.st == ST_ACTIVE) {

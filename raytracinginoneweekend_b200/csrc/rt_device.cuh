@@ -734,6 +734,7 @@ __device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, uint32
 
 // Queue mode, lane 0: the next batch of work -> tile << 32 | first item within the tile (tile >= RT_FEED_NONE: no more work).
 // Slots are opened in order, so a dry slot means that everything behind it is dry too.
+template <uint32_t BATCH>
 __device__ __forceinline__ unsigned long long queue_next_batch(const RtRenderArgs &A)
 {
     uint32_t *ctr = A.feed->slot + A.feed_slots;
@@ -741,7 +742,7 @@ __device__ __forceinline__ unsigned long long queue_next_batch(const RtRenderArg
         const uint32_t k = *reinterpret_cast<volatile uint32_t *>(&A.feed->cur);
         const uint32_t t = (k < A.feed_slots) ? feed_slot_tile(A, k) : RT_FEED_NONE;
         if (t >= RT_FEED_NONE) return (unsigned long long)RT_FEED_NONE << 32;
-        const uint32_t j = atomicAdd(ctr + k, RT_BATCH);
+        const uint32_t j = atomicAdd(ctr + k, BATCH);
         if (j < A.TPS) return ((unsigned long long)t << 32) | j;
         atomicCAS(&A.feed->cur, k, k + 1u);                 // this tile is handed out completely: open the next slot
     }
@@ -750,33 +751,36 @@ __device__ __forceinline__ unsigned long long queue_next_batch(const RtRenderArg
 // Next batch of work items for the warp.  Returns false when there is no more work.
 // QUEUE (template parameter of every render kernel): the work domain is the device-side tile queue instead of the
 // launch's own tile list; separate instantiations, so the single-GPU kernels carry none of the queue code.
-template <bool QUEUE>
+// BATCH: work items a warp takes at once (RT_BATCH = 256 for the brute-force kernels; the LBVH kernel takes 32 -- one per
+// lane -- because its per-path cost is heavy-tailed: a batch is traced by ONE warp, and 256 horizon paths in one warp were
+// a 100 ms tail on a 66 ms multi-GPU frame).
+template <bool QUEUE, uint32_t BATCH>
 __device__ __forceinline__ bool pool_refill(WarpPool &p, const RtRenderArgs &A)
 {
     const uint32_t lane = threadIdx.x & 31u;
     if constexpr (QUEUE) {
         // a batch lies inside ONE tile (TPS is a multiple of RT_BATCH)
         unsigned long long tj = 0ull;
-        if (lane == 0) tj = queue_next_batch(A);
+        if (lane == 0) tj = queue_next_batch<BATCH>(A);
         const uint32_t t = __shfl_sync(RT_FULL, (uint32_t)(tj >> 32), 0);
         const uint32_t j = __shfl_sync(RT_FULL, (uint32_t)tj, 0);
         if (t >= RT_FEED_NONE) return false;
-        RT_DASSERT(t < A.q_ntiles && t < (1u << 23) && j + RT_BATCH <= A.TPS);
-        p.next = j; p.end = (t << 9) | RT_BATCH;
+        RT_DASSERT(t < A.q_ntiles && t < (1u << 23) && j + BATCH <= A.TPS);
+        p.next = j; p.end = (t << 9) | BATCH;
         return true;
     } else {
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(A.work_counter, RT_BATCH);
+        if (lane == 0) base = atomicAdd(A.work_counter, BATCH);
         base = __shfl_sync(RT_FULL, base, 0);
         if (base >= A.total_items) return false;
         p.next = base;
-        p.end = min(base + RT_BATCH, A.total_items);
+        p.end = min(base + BATCH, A.total_items);
         return true;
     }
 }
 
 // Work items for the lanes that want one; `tile` = the item's tile in queue mode (items are then tile-relative).
-template <bool QUEUE>
+template <bool QUEUE, uint32_t BATCH>
 __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, const RtRenderArgs &A, uint32_t &tile)
 {
     const uint32_t lane = threadIdx.x & 31u;
@@ -786,7 +790,7 @@ __device__ __forceinline__ uint32_t pool_take(WarpPool &p, bool want, const RtRe
     while (need) {
         if (QUEUE ? (p.end & 511u) == 0u : p.next >= p.end) {
             if (p.exhausted) break;
-            if (!pool_refill<QUEUE>(p, A)) { p.exhausted = true; break; }
+            if (!pool_refill<QUEUE, BATCH>(p, A)) { p.exhausted = true; break; }
         }
         const uint32_t avail = QUEUE ? (p.end & 511u) : p.end - p.next;
         bool mine = want && item == 0xffffffffu;
@@ -831,7 +835,7 @@ __device__ __forceinline__ unsigned long long to_fixed(float c)
 // One shading pass for one path slot: finish the segment just traced (background / material), hand a new
 // camera sample to the slot if its path ended, draw the random numbers every lane needs in ONE shared
 // Philox loop, then build the next ray.  Must be called by all 32 lanes (pool_take is warp-cooperative).
-template <bool LBVH, bool QUEUE = false, bool PAR = RT_PAR_DEFAULT>
+template <bool LBVH, bool QUEUE = false, bool PAR = RT_PAR_DEFAULT, uint32_t BATCH = RT_BATCH>
 __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *__restrict__ s_sph, PathSlot &S,
                                            float best_t, int best_i, WarpPool &pool, ThreadStats &ts, bool hold = false,
                                            const float *__restrict__ s_rad = nullptr, const uint32_t *__restrict__ s_meta = nullptr,
@@ -903,7 +907,7 @@ __device__ __forceinline__ void shade_slot(const RtRenderArgs &A, const float4 *
     uint32_t ev = S.bounce + 1u;
     for (bool need = want;;) {
         uint32_t qtile = 0u;
-        uint32_t item = pool_take<QUEUE>(pool, need, A, qtile);
+        uint32_t item = pool_take<QUEUE, BATCH>(pool, need, A, qtile);
         if (need) {
             if (item != 0xffffffffu) {
                 // item order: tile-major, then sample, then pixel -- a tile's accumulators (TP * 32 B) stay

@@ -191,15 +191,28 @@ class DeviceQueueFrame:
             with self.torch.cuda.stream(self.stream):
                 self.dist.all_reduce(self.token)
 
-    def render_frame(self, tiles, tile_w, tile_h, spp, max_depth, seed, flags=0):
+    def render_frame(self, tiles, tile_w, tile_h, spp, max_depth, seed, flags=0, trace=None):
+        """trace: optional list; gets five CUDA events (start, cursors acknowledged, rendered, resolved, frame acknowledged)
+        recorded on the stream, for per-phase timing of one rank (bench.py, `ranks[*].phases_ms`)."""
         be = self.be
+
+        def mark():
+            if trace is not None:
+                ev = self.torch.cuda.Event(enable_timing=True)
+                ev.record(self.stream)
+                trace.append(ev)
+        mark()
         be.clear()
         if self.rank == 0:
             be.queue_dev_reset(self.cursors, len(tiles), self.world)
         self._ack()
+        mark()
         be.render_queue(tiles, tile_w, tile_h, self.cursors, self.rank, self.world, spp, max_depth, seed, 0, flags)
+        mark()
         be.resolve_tiles_to(self.frame)
+        mark()
         self._ack()
+        mark()
 
     def close(self):
         be = self.be
