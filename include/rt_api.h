@@ -268,6 +268,9 @@ RT_EXPORT int rt_render_queue(rt_ctx *ctx, const rt_tile *tiles, uint32_t ntiles
 /* rgb8_frame_dev: device pointer to a W*H*3 frame (rank 0's, peer-mapped), or NULL for this context's own RGB8 buffer */
 RT_EXPORT int rt_resolve_tiles_to(rt_ctx *ctx, void *rgb8_frame_dev);
 RT_EXPORT int rt_queue_tiles_rendered(rt_ctx *ctx, uint32_t *count);   /* tiles the last rt_render_queue launch acquired */
+/* the same in acquisition order: tile indices and the device's globaltimer (>> 10: about microseconds) at each acquisition;
+ * at most `cap` entries are written, *count is the total (diagnosis of the stealing schedule) */
+RT_EXPORT int rt_queue_trace(rt_ctx *ctx, uint32_t *tiles, uint32_t *when_us, uint32_t cap, uint32_t *count);
 /* copy the context's device RGB8 buffer to the HOST as it is (no resolve): rank 0 after the peers' stores */
 RT_EXPORT int rt_copy_rgb8(rt_ctx *ctx, uint8_t *dst);
 /* CUDA IPC plumbing for one process per GPU: export a device allocation of this context (the cursors, the RGB8 frame

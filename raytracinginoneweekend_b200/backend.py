@@ -34,7 +34,7 @@ EXPORTS = [
     "rt_stats_reset", "rt_write_ppm", "rt_fp32_peak_probe", "rt_tf32_peak_probe", "rt_filter_info", "rt_debug_sample_ball", "rt_render_progressive",
     "rt_queue_open", "rt_queue_reset", "rt_queue_next", "rt_queue_close",
     "rt_get_stream", "rt_queue_dev_create", "rt_queue_dev_reset", "rt_queue_dev_free", "rt_render_queue",
-    "rt_resolve_tiles_to", "rt_queue_tiles_rendered", "rt_copy_rgb8", "rt_ipc_export", "rt_ipc_import", "rt_ipc_close",
+    "rt_resolve_tiles_to", "rt_queue_tiles_rendered", "rt_queue_trace", "rt_copy_rgb8", "rt_ipc_export", "rt_ipc_import", "rt_ipc_close",
     "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_ctx", "rt_multi_render_frame",
     "rt_multi_render_again", "rt_multi_last_frame",
 ]
@@ -145,6 +145,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_render_queue.argtypes = [vp, vp, u32, u32, u32, C.POINTER(RtRenderParams), vp, u32, u32]
     lib.rt_resolve_tiles_to.argtypes = [vp, vp]
     lib.rt_queue_tiles_rendered.argtypes = [vp, C.POINTER(u32)]
+    lib.rt_queue_trace.argtypes = [vp, vp, vp, u32, C.POINTER(u32)]
     lib.rt_copy_rgb8.argtypes = [vp, vp]
     lib.rt_ipc_export.argtypes = [vp, vp, vp]
     lib.rt_ipc_import.argtypes = [vp, vp, C.POINTER(vp)]
@@ -283,6 +284,13 @@ class Backend:
         n = C.c_uint32(0)
         _check(self.lib, self.lib.rt_queue_tiles_rendered(self.ctx, C.byref(n)))
         return int(n.value)
+
+    def queue_trace(self, cap=65536):
+        """(tile indices, acquisition times in ~us of this GPU's globaltimer) of the last render_queue launch, in order."""
+        tiles = np.zeros(cap, np.uint32); when = np.zeros(cap, np.uint32); n = C.c_uint32(0)
+        _check(self.lib, self.lib.rt_queue_trace(self.ctx, tiles.ctypes.data, when.ctypes.data, cap, C.byref(n)))
+        k = min(cap, int(n.value))
+        return tiles[:k], when[:k]
 
     def copy_rgb8(self):
         out = np.zeros((self.H, self.W, 3), np.uint8)

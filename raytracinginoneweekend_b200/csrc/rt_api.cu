@@ -599,7 +599,7 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         if (want > c->feed_slots) {
             CK(cudaStreamSynchronize(c->stream));
             cudaFree(c->d_feed); c->d_feed = nullptr; c->feed_slots = 0;
-            CK(cudaMalloc((void **)&c->d_feed, sizeof(RtTileFeed) + 2u * (size_t)want * sizeof(uint32_t)));
+            CK(cudaMalloc((void **)&c->d_feed, sizeof(RtTileFeed) + 3u * (size_t)want * sizeof(uint32_t)));
             c->feed_slots = want;
         }
     }
@@ -1095,6 +1095,23 @@ int rt_queue_tiles_rendered(rt_ctx *c, uint32_t *count)
     CK(cudaMemcpy(h.data(), c->d_feed->slot, (size_t)c->feed_slots * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     uint32_t n = 0;
     for (uint32_t v : h) if (v < RT_FEED_NONE) ++n;
+    *count = n;
+    return drain_events(c);
+}
+
+int rt_queue_trace(rt_ctx *c, uint32_t *tiles, uint32_t *when_us, uint32_t cap, uint32_t *count)
+{
+    if (!c || !count || !c->feed_valid) return fail(RT_ERR_INVALID, "rt_queue_trace: no rt_render_queue launch");
+    CK(enter_ctx(c));
+    CK(cudaStreamSynchronize(c->stream));
+    std::vector<uint32_t> h(3u * (size_t)c->feed_slots);
+    CK(cudaMemcpy(h.data(), c->d_feed->slot, h.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    uint32_t n = 0;
+    for (uint32_t k = 0; k < c->feed_slots; ++k)
+        if (h[k] < RT_FEED_NONE) {
+            if (n < cap) { if (tiles) tiles[n] = h[k]; if (when_us) when_us[n] = h[2u * c->feed_slots + k]; }
+            ++n;
+        }
     *count = n;
     return drain_events(c);
 }

@@ -22,7 +22,9 @@
 #endif
 #define RT_BVH_OVF_DEPTH 64
 #ifndef RT_BVH_BATCH
-#define RT_BVH_BATCH 32u            // work items a warp takes at once (see pool_refill: heavy-tailed path cost)
+#define RT_BVH_BATCH RT_BATCH       // work items a warp takes at once.  32 (one per lane) was measured against 256 on 2 GPUs for the
+                                    // 1M-sphere frame: no change (382 vs 386 ms) -- the multi-GPU tail of that frame is single PATHS
+                                    // that run for tens of ms (profiles/r02_trace_c5.log), not batches held by one warp
 #endif
 #ifndef RT_BVH_BRANCHFREE
 #define RT_BVH_BRANCHFREE 0        // 1: push / pop as single predicated shared-memory instructions (measured slower: 795 vs 809 Msamples/s on 1M spheres)

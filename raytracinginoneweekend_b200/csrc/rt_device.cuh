@@ -720,6 +720,9 @@ __device__ __forceinline__ uint32_t feed_slot_tile(const RtRenderArgs &A, uint32
         v = atomicCAS(slot, RT_FEED_EMPTY, RT_FEED_FETCHING);
         if (v == RT_FEED_EMPTY) {
             v = queue_fetch(A);
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            A.feed->slot[2u * A.feed_slots + k] = (uint32_t)(now >> 10);      // acquisition time, ~microseconds (rt_queue_trace)
             __threadfence();
             *reinterpret_cast<volatile uint32_t *>(slot) = v;
             return v;
@@ -751,9 +754,7 @@ __device__ __forceinline__ unsigned long long queue_next_batch(const RtRenderArg
 // Next batch of work items for the warp.  Returns false when there is no more work.
 // QUEUE (template parameter of every render kernel): the work domain is the device-side tile queue instead of the
 // launch's own tile list; separate instantiations, so the single-GPU kernels carry none of the queue code.
-// BATCH: work items a warp takes at once (RT_BATCH = 256 for the brute-force kernels; the LBVH kernel takes 32 -- one per
-// lane -- because its per-path cost is heavy-tailed: a batch is traced by ONE warp, and 256 horizon paths in one warp were
-// a 100 ms tail on a 66 ms multi-GPU frame).
+// BATCH: work items a warp takes at once (RT_BATCH = 256; a template parameter so that a kernel can choose: RT_BVH_BATCH).
 template <bool QUEUE, uint32_t BATCH>
 __device__ __forceinline__ bool pool_refill(WarpPool &p, const RtRenderArgs &A)
 {

@@ -73,7 +73,8 @@ struct RtTileFeed {
     uint32_t drained;                  // set once a fetch found every range dry
     uint32_t pad[2];
     uint32_t slot[1];                  // [nslots] RT_FEED_EMPTY before the launch; afterwards the tiles this GPU rendered
-                                       // followed by ctr[nslots]: items handed out of each slot, zeroed before the launch
+                                       // followed by ctr[nslots]: items handed out of each slot, zeroed before the launch,
+                                       // and when[nslots]: globaltimer >> 10 at the acquisition of the slot (rt_queue_trace)
 };
 
 struct RtRenderArgs {

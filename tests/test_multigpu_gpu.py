@@ -69,8 +69,8 @@ def test_rt_multi_one_process_equals_single_context(be):
             assert sum(info["tiles_per_device"]) == 5 * 6
             again = mb.render_again(spp, 50, seed=4)
             assert np.array_equal(again, want)
-            st = mb.ctx(0).stats()
-            assert st["samples"] > 0
+            # (with one device listed several times the contexts share the GPU: any of them may end up rendering everything)
+            assert sum(mb.ctx(i).stats()["samples"] for i in range(len(devices))) >= W * H * spp
         finally:
             mb.close()
 
