@@ -180,6 +180,23 @@ RT_EXPORT int rt_primary_hits(rt_ctx *ctx, const rt_tile *tile, uint32_t flags,
 RT_EXPORT int rt_closest_hits(rt_ctx *ctx, const float *rays6, uint64_t n, uint32_t flags,
                               int32_t *sphere_index, float *t, float *normal_xyz);
 
+/* The same closest-hit pass for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * No context and no allocation of any kind: the sphere records, the rays and the results are staged
+ * in one file-scope device array of fixed size (csrc/rt_static.cu; about 2.9 MB that every GPU which loads the library
+ * holds until exit), hence the limits below -- larger inputs are rejected with RT_ERR_INVALID and a message, use
+ * rt_closest_hits for them.  spheres_xyzr = n_spheres x {cx, cy, cz, r}; rays6 = n_rays x {o[3], d[3]}; the three outputs
+ * as for rt_closest_hits.  Every pointer may be host OR device memory (unified addressing).  Runs on the CURRENT device, on
+ * cuda_stream (a cudaStream_t of that device; NULL = the default stream), with the parity kernel of RT_FLAG_EXACT: index,
+ * t and normal are bit-identical to rt_closest_hits.  The call returns after the stream has drained unless
+ * RT_STATIC_NO_SYNC is set (then pageable host outputs are not safe to read until the caller synchronises).
+ * All calls on one GPU share the array: calls that overlap on the GPU (two streams or two host threads) race. */
+#define RT_STATIC_MAX_SPHERES 4096u
+#define RT_STATIC_MAX_RAYS 65536u
+#define RT_STATIC_NO_SYNC 1u
+RT_EXPORT int rt_closest_hits_static(const float *spheres_xyzr, uint32_t n_spheres, const float *rays6, uint32_t n_rays,
+                                     int32_t *sphere_index, float *t, float *normal_xyz, void *cuda_stream, uint32_t flags);
+
 /* Resolve: mean = sum / count -> powf(mean, 1/2.2f) -> (uint8)(255*c), tightly packed RGB, row-major,
  * top row first (the reference's texel layout, src/main.cxx:96-100).  dst is HOST memory, W*H*3. */
 RT_EXPORT int rt_readback_rgb8(rt_ctx *ctx, uint8_t *dst);

@@ -37,6 +37,7 @@ EXPORTS = [
     "rt_resolve_tiles_to", "rt_queue_tiles_rendered", "rt_queue_trace", "rt_copy_rgb8", "rt_ipc_export", "rt_ipc_import", "rt_ipc_close",
     "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_ctx", "rt_multi_render_frame",
     "rt_multi_render_again", "rt_multi_last_frame",
+    "rt_closest_hits_static",
 ]
 
 
@@ -157,6 +158,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.rt_multi_render_frame.argtypes = [vp, vp, u32, vp, u32, fp, u32, u32, C.POINTER(RtRenderParams), u32, u32, u32, vp]
     lib.rt_multi_render_again.argtypes = [vp, C.POINTER(RtRenderParams), u32, vp]
     lib.rt_multi_last_frame.argtypes = [vp, C.POINTER(u32), C.POINTER(i32), C.POINTER(C.c_double)]
+    lib.rt_closest_hits_static.argtypes = [vp, u32, vp, u32, vp, vp, vp, vp, u32]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ("rt_last_error", "rt_version", "rt_multi_ctx"):
@@ -510,6 +512,25 @@ class MultiBackend:
         nccl, ms = C.c_int(0), C.c_double(0)
         _check(self.lib, self.lib.rt_multi_last_frame(self.m, tiles, C.byref(nccl), C.byref(ms)))
         return {"tiles_per_device": list(tiles), "nccl": bool(nccl.value), "frame_ms": ms.value}
+
+
+STATIC_MAX_SPHERES, STATIC_MAX_RAYS, STATIC_NO_SYNC = 4096, 65536, 1
+
+
+def closest_hits_static(spheres_xyzr, rays, stream=None, flags=0):
+    """rt_closest_hits_static (include/rt_api.h): closest hit with no context and no allocation -- the scratch is a
+    fixed device array inside the library, so at most STATIC_MAX_SPHERES spheres and STATIC_MAX_RAYS rays per call.
+    Host arrays in, host arrays out; runs on the current CUDA device.  No counterpart in the reference."""
+    lib = load_library()
+    sph = np.ascontiguousarray(spheres_xyzr, np.float32).reshape(-1, 4)
+    rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+    n = rays.shape[0]
+    idx = np.zeros(n, np.int32)
+    tt = np.zeros(n, np.float32)
+    nrm = np.zeros((n, 3), np.float32)
+    _check(lib, lib.rt_closest_hits_static(sph.ctypes.data, sph.shape[0], rays.ctypes.data, n, idx.ctypes.data,
+                                           tt.ctypes.data, nrm.ctypes.data, stream, int(flags)))
+    return idx, tt, nrm
 
 
 def write_ppm(path, rgb8):
