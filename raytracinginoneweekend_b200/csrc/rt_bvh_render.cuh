@@ -26,8 +26,20 @@
                                     // 1M-sphere frame: no change (382 vs 386 ms) -- the multi-GPU tail of that frame is single PATHS
                                     // that run for tens of ms (profiles/r02_trace_c5.log), not batches held by one warp
 #endif
+#ifndef RT_BVH_PATHSTAT
+#define RT_BVH_PATHSTAT 0          // measurement build: > 0 prints every path with more node visits than this (device printf)
+#endif
 #ifndef RT_BVH_BRANCHFREE
 #define RT_BVH_BRANCHFREE 0        // 1: push / pop as single predicated shared-memory instructions (measured slower: 795 vs 809 Msamples/s on 1M spheres)
+#endif
+
+#if RT_BVH_PATHSTAT
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 #endif
 
 struct BvhTrav {
@@ -59,10 +71,30 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     T.node = 0; T.sp = 0; T.best_t = FLT_MAX; T.best_i = -1; T.a = 0.f; T.ix = T.iy = T.iz = 0.f; T.active = false;
     uint32_t ovf[RT_BVH_OVF_DEPTH];
 
+#if RT_BVH_PATHSTAT
+    // measurement build: report every path that visited more than RT_BVH_PATHSTAT nodes (pixel, sample, node visits, bounces,
+    // microseconds from its first to its last segment, end time) -- the heavy tail behind the multi-GPU frame end
+    uint32_t ps_id = 0xffffffffu, ps_nodes0 = 0, ps_bounce = 0;
+    unsigned long long ps_t0 = 0;
+    if (blockIdx.x == 0 && tid == 0) printf("PATHSTAT start %llu\n", globaltimer_ns() / 1000ull);
+#endif
     for (;;) {
         // ---- shade the lanes whose query finished, hand out new work, start their next query
         const bool hold = T.active;
         shade_slot<true, QUEUE, RT_PAR_DEFAULT, RT_BVH_BATCH>(A, nullptr, S, T.best_t, T.best_i, pool, ts, hold);
+#if RT_BVH_PATHSTAT
+        {
+            const uint32_t id = S.st == ST_EMPTY ? 0xffffffffu : S.pix * 1024u + S.smp;
+            if (id != ps_id) {
+                const unsigned long long now = globaltimer_ns();
+                if (ps_id != 0xffffffffu && ts.bvh.nodes - ps_nodes0 > (uint32_t)RT_BVH_PATHSTAT)
+                    printf("PATHSTAT path pix %u smp %u nodes %u bounces %u us %llu end %llu\n", ps_id >> 10, ps_id & 1023u,
+                           ts.bvh.nodes - ps_nodes0, ps_bounce, (now - ps_t0) / 1000ull, now / 1000ull);
+                ps_id = id; ps_nodes0 = ts.bvh.nodes; ps_t0 = now;
+            }
+            ps_bounce = S.bounce;
+        }
+#endif
         if (!hold) {
             T.best_t = FLT_MAX; T.best_i = -1;
             if (S.st == ST_ACTIVE) {
@@ -149,6 +181,9 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
         }
     }
 
+#if RT_BVH_PATHSTAT
+    if (blockIdx.x == 0 && tid == 0) printf("PATHSTAT first_warp_end %llu\n", globaltimer_ns() / 1000ull);
+#endif
     uint32_t v[7] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped, ts.bvh.nodes, ts.bvh.leaves};
 #pragma unroll
     for (int k = 0; k < 7; ++k) {

@@ -20,7 +20,7 @@
 //   reflect/refract/normalize/mix                     src/math.hxx:219-227,294-335
 #pragma once
 #include <cfloat>
-#ifdef RT_TC_PROF
+#if defined(RT_TC_PROF) || RT_BVH_PATHSTAT
 #include <cstdio>
 #endif
 #include "rt_types.h"
