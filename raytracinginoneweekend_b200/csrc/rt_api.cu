@@ -756,7 +756,9 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
 #define RT_RENDER_SELF_QUEUE 1
 #endif
 #ifndef RT_RENDER_SELF_QUEUE_LBVH
-#define RT_RENDER_SELF_QUEUE_LBVH 0     // the LBVH kernel keeps the sample-major order of one W x H tile on a single GPU (0.91 vs 0.80 Gsamples/s)
+#define RT_RENDER_SELF_QUEUE_LBVH 1     // the LBVH kernel too, since it finishes its stragglers cooperatively (rt_bvh_render.cuh: bvh_coop_query):
+                                       // 1M spheres, 1920x1080x256 spp: 569-577 ms through the queue, 600 ms as one sample-major tile
+                                       // (before: 606-640 vs 595-603 -- the tile-major frame happened to end on a few very long paths)
 #endif
     const bool will_lbvh = (p->flags & RT_FLAG_ACCEL_LBVH) ||
                            (!(p->flags & RT_FLAG_ACCEL_BRUTE) && c->n > ((p->flags & RT_FLAG_EXACT) ? RT_BRUTE_MAX_SPHERES : RT_AUTO_LBVH_SPHERES));

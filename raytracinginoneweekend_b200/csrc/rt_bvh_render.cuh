@@ -42,6 +42,94 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 }
 #endif
 
+#ifndef RT_BVH_COOP
+#define RT_BVH_COOP 32             // straggler mode (0 = off): once the warp's work pool is dry and at most this many lanes are still
+                                   // traversing, and have been for RT_BVH_COOP_AFTER loop iterations, the WHOLE warp traverses their rays.
+                                   // Measured on the 1M-sphere frame through the tile queue (one GPU, 256 spp, profiles/r02_coop_ab.log):
+                                   // off 606-640 ms, 4 lanes / 64 iterations 574-578 ms, 32 lanes / 1 iteration (= as soon as the
+                                   // pool is dry) 569 ms
+#endif
+#ifndef RT_BVH_COOP_AFTER
+#define RT_BVH_COOP_AFTER 1
+#endif
+#ifndef RT_BVH_COOP_CAP
+#define RT_BVH_COOP_CAP (RT_BVH_SMEM_DEPTH * 32u)   // entries of the warp's work list (test builds shrink it to exercise the overflow path)
+#endif
+
+// One ray, 32 lanes (bvh_coop_query).  Why: traversal cost is heavy tailed beyond anything a schedule can absorb -- 30 of the
+// 5.3e8 paths of the 1M-sphere frame visit more than 20 000 nodes, the worst 301 812 in four segments (rays that leave the far
+// ground and skim the whole sphere field inside the conservative padding of its boxes), and such a path, alone in its warp at
+// one dependent L2 round trip per node, runs for 389 ms of a 620 ms frame (profiles/r02_pathstat.log); on 8 GPUs the frame
+// ends when the unluckiest GPU's last such path does.
+// How: the warp's 32 stack columns become ONE work list of node indices.  Every round the top min(32, count) nodes are taken,
+// one per lane; a lane tests both children of its node (the same conservative box test, the same leaf test as the sequential
+// traversal), the closest hit so far is merged over the warp as the (t, index) minimum -- the closest hit IS that minimum
+// over all spheres the reference test accepts, so the order in which candidates are met cannot change it, and a box is only
+// ever culled against a bound that is no smaller than the final one -- and the surviving inner children are appended by
+// ballot + popc prefix, far child below near child.  The query restarts from the root with the lane's best hit so far as
+// the bound (what the lane had on its own stack is dropped: the list overwrites the columns).  A list that would overflow
+// gives up (returns false): the caller restarts the sequential traversal from the root, again with the best so far.
+struct BvhCoopResult { float t; int i; uint32_t nodes, leaves; bool fits; };
+// (everything by value: a reference to the kernel's long-lived state would pin that state to local memory)
+__device__ __noinline__ BvhCoopResult bvh_coop_query(const RtDeviceScene &sc, uint32_t *list, float ox, float oy, float oz, float dx, float dy,
+                                                     float dz, float a, float ix, float iy, float iz, float best_t, int best_i)
+{
+    BvhCounters cnt = {0u, 0u};
+    constexpr uint32_t CAP = RT_BVH_COOP_CAP;                // entry i lives at list[(i >> 5) * RT_THREADS + (i & 31)]
+    const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    float bt = best_t; int bi = best_i;
+    uint32_t count = 1;
+    if (lane == 0) list[0] = sc.bvh_root;
+    __syncwarp();
+    bool fits = true;
+    while (count) {
+        const uint32_t w = min(count, 32u);
+        const bool mine = lane < w;
+        uint32_t node = 0;
+        if (mine) { const uint32_t i = count - 1u - lane; node = list[(i >> 5) * RT_THREADS + (i & 31u)]; }
+        count -= w;
+        __syncwarp();                                       // every lane has its node before anyone appends
+        float lt = bt; int li = bi;
+        bool pl = false, pr = false, left_first = true;
+        uint2 ch = make_uint2(0u, 0u);
+        if (mine) {
+            const float4 *np = sc.bvh_nodes + 4 * (size_t)node;
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            ch = make_uint2(__float_as_uint(n3.x), __float_as_uint(n3.y));
+            ++cnt.nodes;
+            float tl, tr;
+            const bool hl = RT_BVH_BOX_L(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, bt, tl);
+            const bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, bt, tr);
+            if (hl && (ch.x >> 31)) RT_BVH_LEAF_L(n0, n1, n2, ch.x, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
+            if (hr && (ch.y >> 31)) RT_BVH_LEAF_R(n0, n1, n2, ch.y, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
+            pl = hl && !(ch.x >> 31); pr = hr && !(ch.y >> 31);
+            left_first = tl <= tr;
+        }
+        if (__any_sync(RT_FULL, lt < bt || li != bi)) {      // (t, index) minimum over the warp; t > 0, so its bits order like t
+            const uint32_t tb = __float_as_uint(lt);
+            const uint32_t tmin = __reduce_min_sync(RT_FULL, tb);
+            bi = (int)__reduce_min_sync(RT_FULL, tb == tmin ? (uint32_t)li : 0xffffffffu);
+            bt = __uint_as_float(tmin);
+        }
+        const uint32_t bl = __ballot_sync(RT_FULL, pl), br = __ballot_sync(RT_FULL, pr);
+        const uint32_t add = (uint32_t)(__popc(bl) + __popc(br));
+        if (count + add > CAP) { fits = false; break; }
+        uint32_t at = count + (uint32_t)(__popc(bl & below) + __popc(br & below));
+        if (pl && pr) {
+            list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first ? ch.y : ch.x;
+            ++at;
+            list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first ? ch.x : ch.y;
+        } else if (pl || pr) {
+            list[(at >> 5) * RT_THREADS + (at & 31u)] = pl ? ch.x : ch.y;
+        }
+        count += add;
+        __syncwarp();
+    }
+    BvhCoopResult r;
+    r.t = bt; r.i = bi; r.nodes = cnt.nodes; r.leaves = cnt.leaves; r.fits = fits;
+    return r;
+}
+
 struct BvhTrav {
     uint32_t node;
     int sp;
@@ -49,6 +137,66 @@ struct BvhTrav {
     float a, ix, iy, iz;
     bool active;
 };
+
+#if RT_BVH_COOP
+// per-warp statistics into the launch's counters (the tail of both k_render_bvh and bvh_straggler_loop)
+__device__ __forceinline__ void bvh_flush_stats(const RtRenderArgs &A, const ThreadStats &ts)
+{
+    uint32_t v[7] = {ts.samples, ts.segments, ts.sky, ts.absorbed, ts.capped, ts.bvh.nodes, ts.bvh.leaves};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        uint32_t x = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(RT_FULL, x, o);
+        if ((threadIdx.x & 31u) == 0 && x) atomicAdd(A.stats + k, (unsigned long long)x);
+    }
+}
+
+// Straggler loop: the rest of a warp's paths once its work pool is dry and only a few long traversals are left -- every
+// closest-hit query by the whole warp.  Out of line and entered once, at the end of the kernel, with the warp's state BY VALUE, so
+// that nothing it needs lengthens a live range in the traversal loop of k_render_bvh (as an inline block it put 6 local-memory
+// loads into every node step).
+template <bool QUEUE>
+__device__ __noinline__ void bvh_straggler_loop(const RtRenderArgs &A, uint32_t *list, PathSlot S, BvhTrav T, WarpPool pool, ThreadStats ts)
+{
+    const RtDeviceScene &sc = A.sc;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        for (uint32_t m = __ballot_sync(RT_FULL, T.active); m; m &= m - 1u) {
+            const int src = __ffs(m) - 1;
+            const float ox = __shfl_sync(RT_FULL, S.ox, src), oy = __shfl_sync(RT_FULL, S.oy, src), oz = __shfl_sync(RT_FULL, S.oz, src);
+            const float dx = __shfl_sync(RT_FULL, S.dx, src), dy = __shfl_sync(RT_FULL, S.dy, src), dz = __shfl_sync(RT_FULL, S.dz, src);
+            const BvhCoopResult r = bvh_coop_query(sc, list, ox, oy, oz, dx, dy, dz, __shfl_sync(RT_FULL, T.a, src),
+                                                   __shfl_sync(RT_FULL, T.ix, src), __shfl_sync(RT_FULL, T.iy, src),
+                                                   __shfl_sync(RT_FULL, T.iz, src), __shfl_sync(RT_FULL, T.best_t, src),
+                                                   __shfl_sync(RT_FULL, T.best_i, src));
+            ts.bvh.nodes += r.nodes; ts.bvh.leaves += r.leaves;
+            if ((int)lane == src) {
+                float bt = r.t; int bi = r.i;
+                if (!r.fits) {
+                    // a work list that overflowed: this lane runs the plain traversal to the end, with the best hit so far as its bound
+                    BvhCounters c2 = {0u, 0u};
+                    closest_hit_lbvh(sc, true, ox, oy, oz, dx, dy, dz, bt, bi, c2, true);
+                    ts.bvh.nodes += c2.nodes; ts.bvh.leaves += c2.leaves;
+                }
+                T.best_t = bt; T.best_i = bi; T.active = false;
+            }
+            __syncwarp();
+        }
+        shade_slot<true, QUEUE, RT_PAR_DEFAULT, RT_BVH_BATCH>(A, nullptr, S, T.best_t, T.best_i, pool, ts, false);
+        T.best_t = FLT_MAX; T.best_i = -1;
+        if (S.st == ST_ACTIVE) {
+            T.a = ray_a(S.dx, S.dy, S.dz);
+            if (T.a > 0.f && T.a < 3.0e38f) {       // d = 0 or non-finite: the reference test finds nothing
+                T.ix = 1.f / S.dx; T.iy = 1.f / S.dy; T.iz = 1.f / S.dz;
+                T.active = true;
+            }
+        }
+        if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
+    }
+    bvh_flush_stats(A, ts);
+}
+#endif
 
 template <bool QUEUE>
 __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __grid_constant__ RtRenderArgs A)
@@ -78,6 +226,9 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
     unsigned long long ps_t0 = 0;
     if (blockIdx.x == 0 && tid == 0) printf("PATHSTAT start %llu\n", globaltimer_ns() / 1000ull);
 #endif
+#if RT_BVH_COOP
+    bool tail = false;                     // warp-uniform: the work pool is dry and only a few long traversals are left
+#endif
     for (;;) {
         // ---- shade the lanes whose query finished, hand out new work, start their next query
         const bool hold = T.active;
@@ -106,13 +257,24 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
             }
         }
         if (!__any_sync(RT_FULL, S.st != ST_EMPTY)) break;
+#if RT_BVH_COOP
+        if (tail) break;
+#endif
 
         // ---- step all running traversals, one node per iteration
         // lanes that could do something else once their query ends: a live path, or a free slot while work remains
         const uint32_t refill = __ballot_sync(RT_FULL, S.st != ST_EMPTY || !pool.exhausted);
+#if RT_BVH_COOP
+        uint32_t lone = 0;                 // consecutive loop iterations with a dry pool and at most RT_BVH_COOP lanes traversing
+#endif
         for (;;) {
             const uint32_t act = __ballot_sync(RT_FULL, T.active);
             if (act == 0u || __popc(~act & refill) >= RT_BVH_IDLE) break;
+#if RT_BVH_COOP
+            if (pool.exhausted && __popc(act) <= RT_BVH_COOP) {
+                if (++lone == (uint32_t)RT_BVH_COOP_AFTER) { tail = true; break; }     // -> straggler loop below
+            } else lone = 0;
+#endif
 #pragma unroll
             for (int step = 0; step < RT_BVH_STEPS; ++step) {
                 if (!T.active) continue;
@@ -181,6 +343,12 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
         }
     }
 
+#if RT_BVH_COOP
+    if (tail) {                            // what is left of this warp's paths: bvh_straggler_loop (it also adds up the statistics)
+        bvh_straggler_loop<QUEUE>(A, s_stack + (tid & ~31u), S, T, pool, ts);
+        return;
+    }
+#endif
 #if RT_BVH_PATHSTAT
     if (blockIdx.x == 0 && tid == 0) printf("PATHSTAT first_warp_end %llu\n", globaltimer_ns() / 1000ull);
 #endif

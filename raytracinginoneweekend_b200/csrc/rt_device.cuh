@@ -645,11 +645,15 @@ __device__ __forceinline__ bool bvh_box_c(float cx, float cy, float cz, float hx
 #define RT_BVH_BOX_R(n0, n1, n2, n3, ...) bvh_box(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, __VA_ARGS__)
 #endif
 
+// keep_best: start from the caller's (best_t, best_i) -- a hit that was already found is a valid bound, the result is the same minimum
 __device__ __forceinline__ void closest_hit_lbvh(const RtDeviceScene &sc, bool live, float ox, float oy, float oz,
-                                                 float dx, float dy, float dz, float &best_t, int &best_i, BvhCounters &cnt)
+                                                 float dx, float dy, float dz, float &best_t, int &best_i, BvhCounters &cnt,
+                                                 bool keep_best = false)
 {
-    best_t = FLT_MAX;
-    best_i = -1;
+    if (!keep_best) {
+        best_t = FLT_MAX;
+        best_i = -1;
+    }
     const float a = ray_a(dx, dy, dz);
     if (!live || !(a > 0.f) || !(a < 3.0e38f)) return;      // d = 0 or non-finite: the reference test finds nothing
     const float ix = 1.f / dx, iy = 1.f / dy, iz = 1.f / dz;
