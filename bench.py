@@ -515,7 +515,7 @@ def run_gpu_arm(args):
         sc = head["scene"]
         accel = {"rtf::k_render_tc": "brute force: tensor-core candidate filter (sphere matrix in shared memory via TMA, "
                                             "accumulators in TMEM) + IEEE reference test on the candidates",
-                 "rtf::k_render_bvh": "GPU-built LBVH (Morton + radix sort + Karras + refit), conservative traversal, IEEE reference "
+                 "rtb::k_render_bvh": "GPU-built LBVH (Morton + radix sort + Karras + refit), conservative traversal, IEEE reference "
                                       "test at the leaves"}.get(head["kernel"], head["kernel"])
         line = {
             "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -126,7 +126,7 @@ enum rt_kernel_id {
     RT_KERNEL_RENDER_TC = 4,         /* rtf::k_render_tc: tensor-core candidate filter, throughput shading (the timed default) */
     RT_KERNEL_RENDER_TC_PARITY = 5,  /* rtx::k_render_tc: the same kernel with the parity shading (bit-identical to the oracle) */
     RT_KERNEL_RENDER_BVH_PARITY = 6, /* rtx::k_render_bvh */
-    RT_KERNEL_RENDER_BVH = 7         /* rtf::k_render_bvh */
+    RT_KERNEL_RENDER_BVH = 7         /* rtb::k_render_bvh: throughput shading, compiled without FMA contraction */
 };
 
 RT_EXPORT const char *rt_last_error(void);

@@ -23,7 +23,7 @@ FLAG_OVERLAP = 1 << 6       # rt_render_tiles: this chunk may run beside the chu
 FLAG_FILTER_FMA = 1 << 3   # candidate filter on the FP32 pipe instead of the tensor cores
 # rt_stats.last_kernel (rt_kernel_id, include/rt_api.h)
 KERNEL_NAMES = {0: "none", 1: "rtx::k_render", 2: "rtf::k_render", 3: "rtf::k_render_small", 4: "rtf::k_render_tc",
-                5: "rtx::k_render_tc", 6: "rtx::k_render_bvh", 7: "rtf::k_render_bvh"}
+                5: "rtx::k_render_tc", 6: "rtx::k_render_bvh", 7: "rtb::k_render_bvh"}
 
 EXPORTS = [
     "rt_last_error", "rt_version", "rt_create", "rt_destroy", "rt_set_stream", "rt_sync", "rt_throttle",

@@ -250,7 +250,8 @@ int occupancy(rt_ctx *c, bool exact, bool lbvh, size_t smem, int *ctas)
     int &slot = c->occ[exact][lbvh];
     if (slot == 0 || c->occ_smem[exact][lbvh] != smem) {
         int v = 0;
-        cudaError_t e = exact ? rtx::render_occupancy(smem, lbvh, &v) : rtf::render_occupancy(smem, lbvh, &v);
+        cudaError_t e = exact ? rtx::render_occupancy(smem, lbvh, &v) : lbvh ? rtb::render_occupancy(smem, lbvh, &v)
+                                                                           : rtf::render_occupancy(smem, lbvh, &v);
         if (e != cudaSuccess) return cuda_fail(e, "render_occupancy");
         if (v < 1) return fail(RT_ERR_INVALID, "render kernel does not fit on an SM (scene too large for shared memory)");
         slot = v;
@@ -718,7 +719,8 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
         cudaError_t e = small ? rtf::launch_render_small(a, grid, st, q)
                         : tensor ? (exact ? rtx::launch_render_tc(a, grid, smem, st, q) : rtf::launch_render_tc(a, grid, smem, st, q))
                         : exact ? rtx::launch_render(a, grid, smem, st, lbvh, q)
-                                : rtf::launch_render(a, grid, smem, st, lbvh, q);
+                        : lbvh ? rtb::launch_render(a, grid, smem, st, lbvh, q)       // throughput LBVH kernel: its own unit, no FMA contraction
+                               : rtf::launch_render(a, grid, smem, st, lbvh, q);
         if (e != cudaSuccess) return cuda_fail(e, "launch_render");
         c->hs.launches += 1;
         c->hs.last_kernel = small ? RT_KERNEL_RENDER_SMALL
@@ -759,6 +761,10 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
 #define RT_RENDER_SELF_QUEUE_LBVH 1     // the LBVH kernel too, since it finishes its stragglers cooperatively (rt_bvh_render.cuh: bvh_coop_query):
                                        // 1M spheres, 1920x1080x256 spp: 569-577 ms through the queue, 600 ms as one sample-major tile
                                        // (before: 606-640 vs 595-603 -- the tile-major frame happened to end on a few very long paths)
+#endif
+#ifndef RT_RENDER_SELF_QUEUE_LBVH_SPP
+#define RT_RENDER_SELF_QUEUE_LBVH_SPP 128   // ... from this many samples per pixel on: at 32 spp the same frame is 8 % faster as one tile
+                                            // (850 vs 784 Msamples/s; 488 spheres through the LBVH at 100 spp: 1340 vs 1275)
 #endif
     const bool will_lbvh = (p->flags & RT_FLAG_ACCEL_LBVH) ||
                            (!(p->flags & RT_FLAG_ACCEL_BRUTE) && c->n > ((p->flags & RT_FLAG_EXACT) ? RT_BRUTE_MAX_SPHERES : RT_AUTO_LBVH_SPHERES));

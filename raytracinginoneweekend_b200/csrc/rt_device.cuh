@@ -29,7 +29,9 @@
 #error "define RT_EXACT to 0 or 1"
 #endif
 
-#if RT_EXACT
+#if defined(RT_NS_OVERRIDE)
+#define RT_NS RT_NS_OVERRIDE       // rt_kernels_bvh.cu: namespace rtb
+#elif RT_EXACT
 #define RT_NS rtx
 #else
 #define RT_NS rtf

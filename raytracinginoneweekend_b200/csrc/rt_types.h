@@ -129,6 +129,11 @@ cudaError_t launch_hits(const RtHitArgs &a, cudaStream_t s, bool lbvh);
 cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
 }
 
+namespace rtb {   // rt_kernels_bvh.cu: the throughput LBVH render kernel, compiled without FMA contraction (lbvh must be true)
+cudaError_t launch_render(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool lbvh, bool queue);
+cudaError_t render_occupancy(size_t smem, bool lbvh, int *ctas_per_sm);
+}
+
 namespace rtf {
 cudaError_t launch_render_tc(const RtRenderArgs &a, int grid, size_t smem, cudaStream_t s, bool queue);
 cudaError_t launch_hits_tc(const RtHitArgs &a, int grid, size_t smem, cudaStream_t s);

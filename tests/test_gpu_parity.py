@@ -381,13 +381,14 @@ def test_tensor_filter_never_drops_a_hit(be, n):
 
 def test_tensor_fma_and_lbvh_kernels_render_the_same_image(be):
     """The three throughput kernels trace the same counter-based paths with the same closest hit (the IEEE reference
-    test decides in all of them: identical hits for identical rays).  Their shading is the same source compiled with FMA
-    contraction into three different kernels, so the low bits of a radiance sample -- and, at a grazing hit, a whole path
-    -- can differ: most accumulator words are bit-equal, the rest agree to rounding, statistics to a few 1e-4."""
+    test decides in all of them: identical hits for identical rays).  Their shading is the same source compiled into three
+    different kernels -- two with FMA contraction, the LBVH kernel without (its unit, rt_kernels_bvh.cu, says why) -- so the
+    low bits of a radiance sample -- and, at a grazing hit, a whole path -- can differ: most accumulator words of the two
+    contracted kernels are bit-equal, about half of the LBVH kernel's, the rest agree to rounding, statistics to a few 1e-4."""
     W, H = 160, 90
     setup(be, scenes.huge_scene(W, H), W, H)
     out = {}
-    for flags, want in ((0, "rtf::k_render_tc"), (FLAG_FILTER_FMA, "rtf::k_render"), (FLAG_LBVH, "rtf::k_render_bvh")):
+    for flags, want in ((0, "rtf::k_render_tc"), (FLAG_FILTER_FMA, "rtf::k_render"), (FLAG_LBVH, "rtb::k_render_bvh")):
         be.clear(); be.reset_stats()
         be.render(64, 50, seed=3, flags=flags)
         out[flags] = (be.readback_accum().astype(np.float64), be.stats())
@@ -396,12 +397,16 @@ def test_tensor_fma_and_lbvh_kernels_render_the_same_image(be):
     a, sa = out[0]
     for flags in (FLAG_FILTER_FMA, FLAG_LBVH):
         b, sb = out[flags]
-        assert (a == b).mean() > 0.80, flags
-        close = np.abs(a - b) <= 1e-6 * np.maximum(a, 1.0)
-        assert close.mean() > 0.995, flags                                   # the rest: a path that took another turn
+        assert (a == b).mean() > (0.30 if flags == FLAG_LBVH else 0.80), flags
+        # rounding differences of up to 50 bounces of float shading: 1e-6 of a sum between the two contracted kernels, 1e-4 against
+        # the uncontracted one
+        close = np.abs(a - b) <= (1e-4 if flags == FLAG_LBVH else 1e-6) * np.maximum(a, 1.0)
+        # the rest: a path that took another turn (a coin or a total reflection decided by the last bit): < 0.5 % of the words
+        # between the contracted kernels, 1.5 % against the uncontracted one (measured)
+        assert close.mean() > (0.97 if flags == FLAG_LBVH else 0.995), flags
         assert abs(a[..., :3].mean() - b[..., :3].mean()) < 1e-3 * a[..., :3].mean()
         for k in ("segments", "sky", "absorbed", "capped"):
-            assert abs(sa[k] - sb[k]) <= 2e-3 * max(sa[k], 1), k
+            assert abs(sa[k] - sb[k]) <= 2e-3 * max(sa[k], 1) + 3 * max(sa[k], 1) ** .5, k      # (+ counting noise of a rare event)
 
 
 # ------------------------------------------------------------------ resolve + e2e call

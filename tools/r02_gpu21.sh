@@ -1,0 +1,10 @@
+#!/bin/bash
+# GPU box, round 2, run 21: single-copy straggler build at 3 CTAs/SM (80 registers) against 4 CTAs/SM (64)
+O=$GRAFT_REPO_ROOT/gpurun_out
+cd "$(dirname "$0")/.."
+for v in default nopark c3 c3np nocoop; do
+  lib=build/variants/$v/librtiow_b200.so; [ $v = default ] && lib=raytracinginoneweekend_b200/librtiow_b200.so
+  echo "== $v"; RTIOW_LIB=$lib python tools/run_config.py --scene synthetic1m --width 1920 --height 1080 --spp 256 --reps 2 | cut -c75-130
+  RTIOW_LIB=$lib python tools/run_config.py --scene huge --width 1280 --height 720 --spp 100 --reps 2 --lbvh | cut -c75-130
+done > $O/r02_coop_ab8.log 2>&1
+cat $O/r02_coop_ab8.log
