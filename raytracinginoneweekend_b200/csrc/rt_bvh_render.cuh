@@ -52,6 +52,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 #ifndef RT_BVH_COOP_AFTER
 #define RT_BVH_COOP_AFTER 1
 #endif
+#ifndef RT_BVH_COOP_WIDE
+#define RT_BVH_COOP_WIDE 1         // nodes a lane takes from the work list per round (bvh_coop_query).  2 (the loads of both in flight
+                                   // together) was measured on the 1M-sphere frame on 8 GPUs: 94.3 vs 87.8 ms -- most queries of a frame's
+                                   // tail are short, and for them the second slot is only more code
+#endif
 #ifndef RT_BVH_COOP_CAP
 #define RT_BVH_COOP_CAP (RT_BVH_SMEM_DEPTH * 32u)   // entries of the warp's work list (test builds shrink it to exercise the overflow path)
 #endif
@@ -83,27 +88,42 @@ __device__ __noinline__ BvhCoopResult bvh_coop_query(const RtDeviceScene &sc, ui
     __syncwarp();
     bool fits = true;
     while (count) {
-        const uint32_t w = min(count, 32u);
-        const bool mine = lane < w;
-        uint32_t node = 0;
-        if (mine) { const uint32_t i = count - 1u - lane; node = list[(i >> 5) * RT_THREADS + (i & 31u)]; }
+        // RT_BVH_COOP_WIDE nodes per lane and round (the loads of all of them are in flight together)
+        constexpr int K = RT_BVH_COOP_WIDE;
+        const uint32_t w = min(count, 32u * K);
+        uint32_t node[K];
+        bool mine[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            mine[k] = lane + 32u * k < w;
+            node[k] = 0u;
+            if (mine[k]) { const uint32_t i = count - 1u - lane - 32u * k; node[k] = list[(i >> 5) * RT_THREADS + (i & 31u)]; }
+        }
         count -= w;
-        __syncwarp();                                       // every lane has its node before anyone appends
+        __syncwarp();                                       // every lane has its nodes before anyone appends
+        float4 n0[K], n1[K], n2[K], n3[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const float4 *np = sc.bvh_nodes + 4 * (size_t)node[k];          // (node 0 for an empty slot: a valid address, never used)
+            n0[k] = __ldg(np); n1[k] = __ldg(np + 1); n2[k] = __ldg(np + 2); n3[k] = __ldg(np + 3);
+        }
         float lt = bt; int li = bi;
-        bool pl = false, pr = false, left_first = true;
-        uint2 ch = make_uint2(0u, 0u);
-        if (mine) {
-            const float4 *np = sc.bvh_nodes + 4 * (size_t)node;
-            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
-            ch = make_uint2(__float_as_uint(n3.x), __float_as_uint(n3.y));
-            ++cnt.nodes;
-            float tl, tr;
-            const bool hl = RT_BVH_BOX_L(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, bt, tl);
-            const bool hr = RT_BVH_BOX_R(n0, n1, n2, n3, ox, oy, oz, ix, iy, iz, sc.bvh_pad0, bt, tr);
-            if (hl && (ch.x >> 31)) RT_BVH_LEAF_L(n0, n1, n2, ch.x, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
-            if (hr && (ch.y >> 31)) RT_BVH_LEAF_R(n0, n1, n2, ch.y, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
-            pl = hl && !(ch.x >> 31); pr = hr && !(ch.y >> 31);
-            left_first = tl <= tr;
+        bool pl[K], pr[K], left_first[K];
+        uint2 ch[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            pl[k] = false; pr[k] = false; left_first[k] = true;
+            ch[k] = make_uint2(__float_as_uint(n3[k].x), __float_as_uint(n3[k].y));
+            if (mine[k]) {
+                ++cnt.nodes;
+                float tl, tr;
+                const bool hl = RT_BVH_BOX_L(n0[k], n1[k], n2[k], n3[k], ox, oy, oz, ix, iy, iz, sc.bvh_pad0, lt, tl);
+                const bool hr = RT_BVH_BOX_R(n0[k], n1[k], n2[k], n3[k], ox, oy, oz, ix, iy, iz, sc.bvh_pad0, lt, tr);
+                if (hl && (ch[k].x >> 31)) RT_BVH_LEAF_L(n0[k], n1[k], n2[k], ch[k].x, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
+                if (hr && (ch[k].y >> 31)) RT_BVH_LEAF_R(n0[k], n1[k], n2[k], ch[k].y, ox, oy, oz, dx, dy, dz, a, lt, li, cnt);
+                pl[k] = hl && !(ch[k].x >> 31); pr[k] = hr && !(ch[k].y >> 31);
+                left_first[k] = tl <= tr;
+            }
         }
         if (__any_sync(RT_FULL, lt < bt || li != bi)) {      // (t, index) minimum over the warp; t > 0, so its bits order like t
             const uint32_t tb = __float_as_uint(lt);
@@ -111,16 +131,26 @@ __device__ __noinline__ BvhCoopResult bvh_coop_query(const RtDeviceScene &sc, ui
             bi = (int)__reduce_min_sync(RT_FULL, tb == tmin ? (uint32_t)li : 0xffffffffu);
             bt = __uint_as_float(tmin);
         }
-        const uint32_t bl = __ballot_sync(RT_FULL, pl), br = __ballot_sync(RT_FULL, pr);
-        const uint32_t add = (uint32_t)(__popc(bl) + __popc(br));
+        // append the surviving inner children: per lane slot K-1 first ... slot 0 last (on top), far child below near child
+        uint32_t add = 0, at = count;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const uint32_t bl = __ballot_sync(RT_FULL, pl[k]), br = __ballot_sync(RT_FULL, pr[k]);
+            add += (uint32_t)(__popc(bl) + __popc(br));
+            at += (uint32_t)(__popc(bl & below) + __popc(br & below));
+        }
         if (count + add > CAP) { fits = false; break; }
-        uint32_t at = count + (uint32_t)(__popc(bl & below) + __popc(br & below));
-        if (pl && pr) {
-            list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first ? ch.y : ch.x;
-            ++at;
-            list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first ? ch.x : ch.y;
-        } else if (pl || pr) {
-            list[(at >> 5) * RT_THREADS + (at & 31u)] = pl ? ch.x : ch.y;
+#pragma unroll
+        for (int k = K - 1; k >= 0; --k) {
+            if (pl[k] && pr[k]) {
+                list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first[k] ? ch[k].y : ch[k].x;
+                ++at;
+                list[(at >> 5) * RT_THREADS + (at & 31u)] = left_first[k] ? ch[k].x : ch[k].y;
+                ++at;
+            } else if (pl[k] || pr[k]) {
+                list[(at >> 5) * RT_THREADS + (at & 31u)] = pl[k] ? ch[k].x : ch[k].y;
+                ++at;
+            }
         }
         count += add;
         __syncwarp();
