@@ -472,7 +472,8 @@ def run_gpu_arm(args):
             ach = compulsory / (ms * 1e-3) / 1e9
             requested = (st["node_visits"] * 64.0 + st["sphere_tests"] * 16.0) / steps
             return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
-                    "kernel": f"{kernel} (persistent bounce loop, resumable LBVH traversal, stacks in shared memory)",
+                    "kernel": f"{kernel} (persistent bounce loop, resumable LBVH traversal, stacks in shared memory; a warp whose work pool is dry "
+                              "finishes its last queries cooperatively, one ray on 32 lanes)",
                     "peak_source": peak_src,
                     "byte_model": "compulsory DRAM bytes per launch: (n-1) nodes * 64 B + n sphere records * 28 B + W*H*32 B of accumulators",
                     "note": "not HBM bound (frac << 1 on purpose): the tree is L2-resident; the kernel is issue bound -- 71 % issue-active at "
@@ -516,7 +517,7 @@ def run_gpu_arm(args):
         accel = {"rtf::k_render_tc": "brute force: tensor-core candidate filter (sphere matrix in shared memory via TMA, "
                                             "accumulators in TMEM) + IEEE reference test on the candidates",
                  "rtb::k_render_bvh": "GPU-built LBVH (Morton + radix sort + Karras + refit), conservative traversal, IEEE reference "
-                                      "test at the leaves"}.get(head["kernel"], head["kernel"])
+                                      "test at the leaves; stragglers finished by whole warps (DESIGN 6)"}.get(head["kernel"], head["kernel"])
         line = {
             "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

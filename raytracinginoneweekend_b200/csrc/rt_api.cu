@@ -768,7 +768,7 @@ int rt_render(rt_ctx *c, const rt_tile *tile, const rt_render_params *p)
 #endif
     const bool will_lbvh = (p->flags & RT_FLAG_ACCEL_LBVH) ||
                            (!(p->flags & RT_FLAG_ACCEL_BRUTE) && c->n > ((p->flags & RT_FLAG_EXACT) ? RT_BRUTE_MAX_SPHERES : RT_AUTO_LBVH_SPHERES));
-    if (RT_RENDER_SELF_QUEUE && (RT_RENDER_SELF_QUEUE_LBVH || !will_lbvh) && npx >= 4ull * kTw * kTh &&
+    if (RT_RENDER_SELF_QUEUE && (!will_lbvh || (RT_RENDER_SELF_QUEUE_LBVH && p->spp >= RT_RENDER_SELF_QUEUE_LBVH_SPP)) && npx >= 4ull * kTw * kTh &&
         !(p->flags & (RT_FLAG_OVERLAP | RT_FLAG_FILTER_CHECK)) &&
         (unsigned long long)kTw * kTh * p->spp < (1ull << 31) &&
         ((unsigned long long)(tile->w + kTw - 1) / kTw) * ((tile->h + kTh - 1) / kTh) <= kTileRing) {

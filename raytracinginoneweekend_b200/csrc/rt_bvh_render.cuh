@@ -43,14 +43,15 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 #endif
 
 #ifndef RT_BVH_COOP
-#define RT_BVH_COOP 32             // straggler mode (0 = off): once the warp's work pool is dry and at most this many lanes are still
+#define RT_BVH_COOP 4              // straggler mode (0 = off): once the warp's work pool is dry and at most this many lanes are still
                                    // traversing, and have been for RT_BVH_COOP_AFTER loop iterations, the WHOLE warp traverses their rays.
-                                   // Measured on the 1M-sphere frame through the tile queue (one GPU, 256 spp, profiles/r02_coop_ab.log):
-                                   // off 606-640 ms, 4 lanes / 64 iterations 574-578 ms, 32 lanes / 1 iteration (= as soon as the
-                                   // pool is dry) 569 ms
+                                   // Entering as soon as the pool is dry (32 lanes / 1 iteration) serialises the many short queries of
+                                   // a frame's end.  Msamples/s, 1M spheres at 32 spp | at 256 spp | 488 spheres through the LBVH
+                                   // (profiles/r02_coop_ab11.log):  32/1: 765 | 930 | 1181   8/16: 800 | 924 | 1282   4/64: 804 | 926 | 1286
+                                   // 2/256: 819 | 926 | 1280   off: 846 | 885 | 1345 (the short frames pay ~4 % for the mode)
 #endif
 #ifndef RT_BVH_COOP_AFTER
-#define RT_BVH_COOP_AFTER 1
+#define RT_BVH_COOP_AFTER 64
 #endif
 #ifndef RT_BVH_COOP_WIDE
 #define RT_BVH_COOP_WIDE 1         // nodes a lane takes from the work list per round (bvh_coop_query).  2 (the loads of both in flight
