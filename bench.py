@@ -464,7 +464,7 @@ def run_gpu_arm(args):
             # from DRAM once per launch (the tree: (n-1) nodes x 64 B, the sphere records: n x 28 B, the accumulators: W*H*32 B)
             # against the measured HBM copy bandwidth -- a fraction of a per cent.  The SMs REQUEST node_visits x 64 B + leaf
             # tests x 16 B (SURVEY 8(d)'s model, 7-8 TB/s here), served by L1/L2 (ncu: L2 hit rate 87 %, DRAM ~30 GB/s); the limiter
-            # is issue slots (ncu: 71 % issue-active, 15 of 32 lanes per instruction; profiles/r01_ncu_k_render_bvh_center.json).
+            # is issue slots (ncu: 71 % issue-active, 16 of 32 lanes per instruction, L2 hit rate 93 %; profiles/r02_ncu_k_render_bvh.json).
             hbm = float(measured_peaks().get("hbm_gbs", 0) or 0)
             peak_src = "MEASURED_PEAKS.json hbm_gbs" if hbm else "fallback 6550 GB/s (B200_PROFILING.md)"
             hbm = hbm or 6550.0
@@ -477,7 +477,7 @@ def run_gpu_arm(args):
                     "peak_source": peak_src,
                     "byte_model": "compulsory DRAM bytes per launch: (n-1) nodes * 64 B + n sphere records * 28 B + W*H*32 B of accumulators",
                     "note": "not HBM bound (frac << 1 on purpose): the tree is L2-resident; the kernel is issue bound -- 71 % issue-active at "
-                            "15 of 32 lanes (ncu, profiles/r01_ncu_k_render_bvh_center.json)",
+                            "16 of 32 lanes (ncu, profiles/r02_ncu_k_render_bvh.json)",
                     "l2_request_model": {"bytes_per_launch": requested, "GBps": requested / (ms * 1e-3) / 1e9,
                                          "model": "node_visits * 64 B + leaf_tests * 16 B (device counters): what the SMs request, served by L1/L2"},
                     "node_visits_per_segment": st["node_visits"] / max(1, st["segments"]),
