@@ -49,6 +49,23 @@ def test_no_cpu_fallback():
         backend.Backend(0)
 
 
+def test_static_entry_point_refuses_without_a_gpu():
+    """rt_closest_hits_static (no context, no allocation): without a usable GPU it fails with a message, before any launch;
+    its size limits are checked before the device is touched."""
+    import numpy as np
+    import torch
+    from raytracinginoneweekend_b200 import backend
+    sph, ray = np.float32([[0, 0, -1, .5]]), np.float32([[0, 0, 0, 0, 0, -1]])
+    with pytest.raises(backend.RtError, match="RT_STATIC_MAX_SPHERES"):
+        backend.closest_hits_static(np.tile(sph, (backend.STATIC_MAX_SPHERES + 1, 1)), ray)
+    with pytest.raises(backend.RtError, match="RT_STATIC_MAX_RAYS"):
+        backend.closest_hits_static(sph, np.tile(ray, (backend.STATIC_MAX_RAYS + 1, 1)))
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; the refusal path is covered on the CPU runner")
+    with pytest.raises(backend.RtError, match="rt_closest_hits_static: cuda"):
+        backend.closest_hits_static(sph, ray)
+
+
 def test_product_never_imports_oracle():
     pkg = os.path.join(ROOT, "raytracinginoneweekend_b200")
     for dirpath, _, files in os.walk(pkg):
