@@ -72,10 +72,14 @@ enum {
                                      rt_render / rt_render_tiles / rt_render_progressive / rt_render_frame only. */
     /* neither accel flag: parity build -- brute force up to RT_BRUTE_MAX_SPHERES, LBVH above; throughput build -- brute
        force (tensor-core filter) up to RT_AUTO_LBVH_SPHERES, LBVH above (same image: the LBVH returns the brute-force hit) */,
-    RT_FLAG_OVERLAP = 1u << 6     /* rt_render_tiles only: this launch may run BESIDE the rt_render_tiles launches queued before it
+    RT_FLAG_OVERLAP = 1u << 6,    /* rt_render_tiles only: this launch may run BESIDE the rt_render_tiles launches queued before it
                                      (they alternate between two internal streams, so the tail of one persistent launch is
                                      filled by the next).  The caller promises disjoint tiles within a frame, as the multi-GPU
                                      tile scheduler does; every other call on the context is ordered after all of them. */
+    RT_FLAG_TEST_STRAGGLERS = 1u << 7 /* test hook, LBVH render kernels only: a warp enters its straggler mode (the remaining closest-hit
+                                     queries are traversed by the whole warp) the moment its work pool is dry instead of
+                                     waiting until at most four lanes are left, and the odd warps of a CTA get a work list of 8 entries,
+                                     so that their queries overflow into the fallback.  The image must not change by a bit. */
 };
 #define RT_BRUTE_MAX_SPHERES 8192u   /* parity kernels; the throughput kernel with the FMA-chain filter fits about 5 800 spheres in
                                         shared memory -- beyond that RT_FLAG_ACCEL_BRUTE fails with a clear message and the

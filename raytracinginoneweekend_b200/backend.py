@@ -20,6 +20,7 @@ FLAG_LBVH = 1 << 2
 FLAG_FILTER_CHECK = 1 << 4  # count segments whose filtered closest hit differs from the unfiltered one (stats: filter_misses)
 FLAG_BOOK_OPTICS = 1 << 5   # opt-in textbook optics (Snell refraction, eye-relative camera rays, disk lens, [0,1] sky blend)
 FLAG_OVERLAP = 1 << 6       # rt_render_tiles: this chunk may run beside the chunks queued before it (disjoint tiles; two internal streams)
+FLAG_TEST_STRAGGLERS = 1 << 7  # test hook: LBVH kernels enter the straggler mode as soon as a warp's pool is dry; odd warps overflow their work list
 FLAG_FILTER_FMA = 1 << 3   # candidate filter on the FP32 pipe instead of the tensor cores
 # rt_stats.last_kernel (rt_kernel_id, include/rt_api.h)
 KERNEL_NAMES = {0: "none", 1: "rtx::k_render", 2: "rtf::k_render", 3: "rtf::k_render_small", 4: "rtf::k_render_tc",

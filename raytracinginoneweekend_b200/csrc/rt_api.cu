@@ -690,6 +690,10 @@ static int render_tiles_impl(rt_ctx *c, const rt_tile *tiles, uint32_t ntiles, u
     a.check = (p->flags & RT_FLAG_FILTER_CHECK) ? 1u : 0u;
     a.book = (p->flags & RT_FLAG_BOOK_OPTICS) ? 1u : 0u;
     a.smem_mats = smem_mats ? 1u : 0u;
+    const bool test_stragglers = (p->flags & RT_FLAG_TEST_STRAGGLERS) != 0;
+    a.coop_lanes = test_stragglers ? 32u : (uint32_t)RT_BVH_COOP;
+    a.coop_after = test_stragglers ? 1u : (uint32_t)RT_BVH_COOP_AFTER;
+    a.coop_cap_odd = test_stragglers ? 8u : (uint32_t)RT_BVH_COOP_CAP;
     if (qm) {
         a.feed = c->d_feed; a.feed_slots = c->feed_slots;
         a.q_cursors = qm->cursors; a.q_rank = qm->rank; a.q_nranks = qm->nranks; a.q_ntiles = ntiles;

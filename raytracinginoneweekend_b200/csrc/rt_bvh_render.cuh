@@ -42,24 +42,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 }
 #endif
 
-#ifndef RT_BVH_COOP
-#define RT_BVH_COOP 4              // straggler mode (0 = off): once the warp's work pool is dry and at most this many lanes are still
-                                   // traversing, and have been for RT_BVH_COOP_AFTER loop iterations, the WHOLE warp traverses their rays.
-                                   // Entering as soon as the pool is dry (32 lanes / 1 iteration) serialises the many short queries of
-                                   // a frame's end.  Msamples/s, 1M spheres at 32 spp | at 256 spp | 488 spheres through the LBVH
-                                   // (profiles/r02_coop_ab11.log):  32/1: 765 | 930 | 1181   8/16: 800 | 924 | 1282   4/64: 804 | 926 | 1286
-                                   // 2/256: 819 | 926 | 1280   off: 846 | 885 | 1345 (the short frames pay ~4 % for the mode)
-#endif
-#ifndef RT_BVH_COOP_AFTER
-#define RT_BVH_COOP_AFTER 64
-#endif
+// RT_BVH_COOP / RT_BVH_COOP_AFTER / RT_BVH_COOP_CAP: rt_types.h (the host passes them in RtRenderArgs; RT_FLAG_TEST_STRAGGLERS overrides them)
 #ifndef RT_BVH_COOP_WIDE
 #define RT_BVH_COOP_WIDE 1         // nodes a lane takes from the work list per round (bvh_coop_query).  2 (the loads of both in flight
                                    // together) was measured on the 1M-sphere frame on 8 GPUs: 94.3 vs 87.8 ms -- most queries of a frame's
                                    // tail are short, and for them the second slot is only more code
-#endif
-#ifndef RT_BVH_COOP_CAP
-#define RT_BVH_COOP_CAP (RT_BVH_SMEM_DEPTH * 32u)   // entries of the warp's work list (test builds shrink it to exercise the overflow path)
 #endif
 
 // One ray, 32 lanes (bvh_coop_query).  Why: traversal cost is heavy tailed beyond anything a schedule can absorb -- 30 of the
@@ -77,11 +64,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
 // gives up (returns false): the caller restarts the sequential traversal from the root, again with the best so far.
 struct BvhCoopResult { float t; int i; uint32_t nodes, leaves; bool fits; };
 // (everything by value: a reference to the kernel's long-lived state would pin that state to local memory)
-__device__ __noinline__ BvhCoopResult bvh_coop_query(const RtDeviceScene &sc, uint32_t *list, float ox, float oy, float oz, float dx, float dy,
-                                                     float dz, float a, float ix, float iy, float iz, float best_t, int best_i)
+__device__ __noinline__ BvhCoopResult bvh_coop_query(const RtDeviceScene &sc, uint32_t *list, uint32_t CAP, float ox, float oy, float oz, float dx,
+                                                     float dy, float dz, float a, float ix, float iy, float iz, float best_t, int best_i)
 {
     BvhCounters cnt = {0u, 0u};
-    constexpr uint32_t CAP = RT_BVH_COOP_CAP;                // entry i lives at list[(i >> 5) * RT_THREADS + (i & 31)]
+    // CAP: entries of the work list; entry i lives at list[(i >> 5) * RT_THREADS + (i & 31)]
     const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
     float bt = best_t; int bi = best_i;
     uint32_t count = 1;
@@ -192,12 +179,14 @@ __device__ __noinline__ void bvh_straggler_loop(const RtRenderArgs &A, uint32_t 
 {
     const RtDeviceScene &sc = A.sc;
     const uint32_t lane = threadIdx.x & 31u;
+    // entries of the work list: all of the warp's stack columns; RT_FLAG_TEST_STRAGGLERS gives the odd warps of a CTA 8 (every query overflows)
+    const uint32_t cap = min(((threadIdx.x >> 5) & 1u) ? A.coop_cap_odd : (uint32_t)RT_BVH_COOP_CAP, (uint32_t)(RT_BVH_SMEM_DEPTH * 32u));
     for (;;) {
         for (uint32_t m = __ballot_sync(RT_FULL, T.active); m; m &= m - 1u) {
             const int src = __ffs(m) - 1;
             const float ox = __shfl_sync(RT_FULL, S.ox, src), oy = __shfl_sync(RT_FULL, S.oy, src), oz = __shfl_sync(RT_FULL, S.oz, src);
             const float dx = __shfl_sync(RT_FULL, S.dx, src), dy = __shfl_sync(RT_FULL, S.dy, src), dz = __shfl_sync(RT_FULL, S.dz, src);
-            const BvhCoopResult r = bvh_coop_query(sc, list, ox, oy, oz, dx, dy, dz, __shfl_sync(RT_FULL, T.a, src),
+            const BvhCoopResult r = bvh_coop_query(sc, list, cap, ox, oy, oz, dx, dy, dz, __shfl_sync(RT_FULL, T.a, src),
                                                    __shfl_sync(RT_FULL, T.ix, src), __shfl_sync(RT_FULL, T.iy, src),
                                                    __shfl_sync(RT_FULL, T.iz, src), __shfl_sync(RT_FULL, T.best_t, src),
                                                    __shfl_sync(RT_FULL, T.best_i, src));
@@ -302,8 +291,8 @@ __global__ void __launch_bounds__(RT_THREADS, RT_BVH_CTAS) k_render_bvh(const __
             const uint32_t act = __ballot_sync(RT_FULL, T.active);
             if (act == 0u || __popc(~act & refill) >= RT_BVH_IDLE) break;
 #if RT_BVH_COOP
-            if (pool.exhausted && __popc(act) <= RT_BVH_COOP) {
-                if (++lone == (uint32_t)RT_BVH_COOP_AFTER) { tail = true; break; }     // -> straggler loop below
+            if (pool.exhausted && (uint32_t)__popc(act) <= A.coop_lanes) {             // (RT_BVH_COOP / RT_BVH_COOP_AFTER unless a test overrides them)
+                if (++lone >= A.coop_after) { tail = true; break; }                    // -> straggler loop below
             } else lone = 0;
 #endif
 #pragma unroll

@@ -104,6 +104,10 @@ struct RtRenderArgs {
     uint32_t feed_slots;
     uint32_t *q_cursors;         // RT_QUEUE_STRIDE-strided range cursors in rank 0's memory (system-scope atomics)
     uint32_t q_rank, q_nranks, q_ntiles;
+    // straggler mode of k_render_bvh (rt_bvh_render.cuh); at the END of the struct: the other kernels' parameter offsets stay put
+    uint32_t coop_lanes;         // enter once the pool is dry and at most this many lanes still traverse (0 = never) ...
+    uint32_t coop_after;         // ... for this many iterations of the traversal loop
+    uint32_t coop_cap_odd;       // work-list entries of the odd warps of a CTA (RT_FLAG_TEST_STRAGGLERS: 8; else the full list)
 };
 
 struct RtHitArgs {
@@ -150,6 +154,20 @@ cudaError_t launch_sample_ball(float *out, unsigned long long n, uint32_t key0, 
 #ifndef RT_BVH_SMEM_DEPTH
 #define RT_BVH_SMEM_DEPTH 40       // levels of the LBVH traversal stack kept in shared memory (k_render_bvh; rt_common.cu sizes it); deeper levels
                                    // go to a local-memory overflow, so smaller values only change speed (and test the overflow)
+#endif
+#ifndef RT_BVH_COOP
+#define RT_BVH_COOP 4              // straggler mode (0 = off): once the warp's work pool is dry and at most this many lanes are still
+                                   // traversing, and have been for RT_BVH_COOP_AFTER loop iterations, the WHOLE warp traverses their rays.
+                                   // Entering as soon as the pool is dry (32 lanes / 1 iteration) serialises the many short queries of
+                                   // a frame's end.  Msamples/s, 1M spheres at 32 spp | at 256 spp | 488 spheres through the LBVH
+                                   // (profiles/r02_coop_ab11.log):  32/1: 765 | 930 | 1181   8/16: 800 | 924 | 1282   4/64: 804 | 926 | 1286
+                                   // 2/256: 819 | 926 | 1280   off: 846 | 885 | 1345 (the short frames pay ~4 % for the mode)
+#endif
+#ifndef RT_BVH_COOP_AFTER
+#define RT_BVH_COOP_AFTER 64
+#endif
+#ifndef RT_BVH_COOP_CAP
+#define RT_BVH_COOP_CAP (RT_BVH_SMEM_DEPTH * 32u)   // entries of the warp's work list (test builds shrink it to exercise the overflow path)
 #endif
 #ifndef RT_BVH_CENTER
 #define RT_BVH_CENTER 1     // 1: LBVH nodes hold child boxes as centre + half extent (+ L1 half extent): the padded slab test needs 34 instead of 42 FP32 instructions

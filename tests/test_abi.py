@@ -34,7 +34,8 @@ def test_python_flags_match_the_header():
     assert len(header) >= 7 and len(set(header.values())) == len(header)
     mine = {"EXACT": backend.FLAG_EXACT, "ACCEL_BRUTE": backend.FLAG_BRUTE, "ACCEL_LBVH": backend.FLAG_LBVH,
             "FILTER_FMA": backend.FLAG_FILTER_FMA, "FILTER_CHECK": backend.FLAG_FILTER_CHECK,
-            "BOOK_OPTICS": backend.FLAG_BOOK_OPTICS, "OVERLAP": backend.FLAG_OVERLAP}
+            "BOOK_OPTICS": backend.FLAG_BOOK_OPTICS, "OVERLAP": backend.FLAG_OVERLAP,
+            "TEST_STRAGGLERS": backend.FLAG_TEST_STRAGGLERS}
     assert mine == {k: header[k] for k in mine}
     assert multigpu.FLAG_OVERLAP == header["OVERLAP"]
 

@@ -636,6 +636,42 @@ def test_lbvh_render_equals_brute_render(be):
     assert_bits_equal(be.readback_accum(), a, "huge-scene accumulators")
 
 
+@pytest.mark.parametrize("exact", [FLAG_EXACT, 0], ids=["parity-build", "throughput-build"])
+def test_lbvh_straggler_mode_does_not_change_a_bit(be, port, exact):
+    """k_render_bvh finishes a warp's last closest-hit queries with the whole warp (one ray on 32 lanes, a shared work list;
+    DESIGN section 6).  On small frames the mode is rarely entered, so RT_FLAG_TEST_STRAGGLERS forces it from the moment a
+    warp's work pool is dry -- most of a small frame -- and gives the odd warps of every CTA a work list of 8 entries, so that
+    their queries overflow into the fallback.  The accumulators must not change by a bit: the closest hit is the (t, index)
+    minimum whatever the order in which candidates are met, and the throughput LBVH kernel is compiled without FMA
+    contraction so that both of its shading sites are the same arithmetic.  Parity build: equal to the oracle as well."""
+    from raytracinginoneweekend_b200.backend import FLAG_TEST_STRAGGLERS
+    for sc, W, H, spp, seed in ((scenes.synthetic_scene(n_side=40, width=96, height=54), 96, 54, 4, 11),
+                                (scenes.huge_scene(160, 90), 160, 90, 5, 3),
+                                (scenes.synthetic_scene(n_side=141, width=128, height=72), 128, 72, 2, 7)):
+        setup(be, sc, W, H)
+        be.render(spp, 50, seed=seed, flags=exact | FLAG_LBVH)
+        plain, st_plain = be.readback_accum().copy(), be.stats()
+        be.clear(); be.reset_stats()
+        be.render(spp, 50, seed=seed, flags=exact | FLAG_LBVH | FLAG_TEST_STRAGGLERS)
+        forced, st_forced = be.readback_accum(), be.stats()
+        assert_bits_equal(forced, plain, f"accumulators, straggler mode forced ({sc.name})")
+        for k in ("samples", "segments", "sky", "absorbed", "capped"):
+            assert st_forced[k] == st_plain[k], k
+        assert st_forced["node_visits"] > 0
+        if exact and sc.n < 5000:
+            o = port.render(sc, W, H, spp, 50, seed, nthreads=64, rng=RNG_PHILOX, want_fixed=True)
+            assert_bits_equal(forced[..., :3], o["fixed"], f"32.32 radiance sums against the oracle ({sc.name})")
+    # the same through the tile lists of the multi-GPU path (queue instantiation is covered by test_multigpu_gpu.py)
+    from raytracinginoneweekend_b200.multigpu import make_tiles
+    sc, W, H = scenes.synthetic_scene(n_side=40, width=96, height=54), 96, 54
+    setup(be, sc, W, H)
+    be.render(3, 50, seed=5, flags=exact | FLAG_LBVH)
+    plain = be.readback_accum().copy()
+    be.clear()
+    be.render_tiles(make_tiles(W, H, 32, 16), 32, 16, 3, 50, seed=5, flags=exact | FLAG_LBVH | FLAG_TEST_STRAGGLERS)
+    assert_bits_equal(be.readback_accum(), plain, "tile list, straggler mode forced")
+
+
 def test_lbvh_thin_deep_tree_equals_brute_force(be):
     """Sphere centres in geometric progression (a long, thin Karras tree) plus a random cloud: the resumable traversal
     of the render kernel and the one-shot traversal of rt_closest_hits must agree with brute force bit for bit.
