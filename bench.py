@@ -471,7 +471,17 @@ def run_gpu_arm(args):
             compulsory = (sc.n - 1) * 64.0 + sc.n * 28.0 + W * H * 32.0
             ach = compulsory / (ms * 1e-3) / 1e9
             requested = (st["node_visits"] * 64.0 + st["sphere_tests"] * 16.0) / steps
-            return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic,
+            cap = {}
+            try:
+                cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json"))).get("k_render_bvh", {})
+            except Exception:
+                pass
+            return {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
+                    "traffic": None,       # the committed ncu capture is of a smaller launch (see ncu_capture): not this launch's bytes
+                    "ncu_capture": {"dram_bytes_of_the_captured_launch": cap.get("dram_bytes_per_launch"), "what": cap.get("source"),
+                                    "issue_active_pct": cap.get("issue_active_pct"), "lanes_per_instruction": cap.get("lanes_per_instruction")},
+                    "issue_slots": {"frac": (cap.get("issue_active_pct") or 0) / 100.0,
+                                    "note": "the bound that matters: share of cycles in which a scheduler issues (ncu); 16 of 32 lanes per instruction"},
                     "kernel": f"{kernel} (persistent bounce loop, resumable LBVH traversal, stacks in shared memory; a warp whose work pool is dry "
                               "finishes its last queries cooperatively, one ray on 32 lanes)",
                     "peak_source": peak_src,
