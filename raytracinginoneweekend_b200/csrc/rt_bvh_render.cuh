@@ -1,5 +1,6 @@
-// rt_bvh_render.cuh -- persistent bounce loop over the GPU-built LBVH with a RESUMABLE traversal.
-// Included by rt_device.cuh in both arithmetic builds.
+// rt_bvh_render.cuh -- persistent bounce loop over the GPU-built LBVH with a RESUMABLE traversal and a cooperative end game.
+// Included by rt_device.cuh: rtx (parity shading, rt_kernels_exact.cu) and rtb (throughput shading, rt_kernels_bvh.cu -- compiled
+// without FMA contraction: the kernel shades at two sites, and they must be the same arithmetic).
 //
 // Traversal lengths are heavy tailed (sky rays leave after a handful of nodes, rays that skim the sphere field visit
 // hundreds), so "every lane traverses its ray to the end, then the warp shades" keeps 6 of 32 lanes busy (ncu,
@@ -9,6 +10,8 @@
 // The stack lives in shared memory ([depth][thread], conflict free); depths beyond RT_BVH_SMEM_DEPTH (never seen on
 // Morton trees of the test scenes) go to a local-memory overflow so the result never depends on the stack size.
 // Semantics are those of closest_hit_lbvh (conservative boxes, reference test at the leaves, (t, index) order).
+// Once a warp's work pool is dry and only a few lanes still traverse, the WHOLE warp finishes each remaining query
+// (bvh_coop_query, bvh_straggler_loop below): single paths of 10^5 node visits were the end of every multi-GPU frame.
 #pragma once
 
 #ifndef RT_BVH_IDLE
