@@ -1054,8 +1054,13 @@ int rt_queue_dev_create(rt_ctx *c, void **cursors)
 {
     if (!c || !cursors) return fail(RT_ERR_INVALID, "rt_queue_dev_create: NULL argument");
     CK(cudaSetDevice(c->device));
+    *cursors = nullptr;
     CK(cudaMalloc(cursors, (size_t)RT_QUEUE_SLOTS * RT_QUEUE_STRIDE * sizeof(uint32_t)));
-    CK(cudaMemset(*cursors, 0, (size_t)RT_QUEUE_SLOTS * RT_QUEUE_STRIDE * sizeof(uint32_t)));
+    cudaError_t e = cudaMemset(*cursors, 0, (size_t)RT_QUEUE_SLOTS * RT_QUEUE_STRIDE * sizeof(uint32_t));
+    if (e != cudaSuccess) {
+        cudaFree(*cursors); *cursors = nullptr;          // nothing is handed out half-made
+        return cuda_fail(e, "rt_queue_dev_create: cudaMemset");
+    }
     return RT_OK;
 }
 
